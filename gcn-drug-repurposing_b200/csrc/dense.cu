@@ -1,0 +1,242 @@
+// dense.cu — the dense half of GSS_GNNLayer / ResidualGraphConvolutionalNetwork:
+// fused layer transform (two Linear + bias + ELU + residual), row normalisation and the
+// backward pieces autograd derives for them.  Reference: modules/model.py:163-175,197-207.
+#include "gemm_simt.cuh"
+
+namespace gdr {
+
+// ---- F.normalize(x, dim=1): one warp per row ----------------------------------------------
+__global__ void __launch_bounds__(256)
+row_normalize_fwd_kernel(const float *__restrict__ x, int64_t n, int64_t d, float *__restrict__ h,
+                         float *__restrict__ norm) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (row >= n) return;
+  const float *xr = x + row * d;
+  float ss = 0.f;
+  for (int64_t c = lane * 4; c < d; c += 128) {
+    const float4 v = ldg_f4(xr + c);
+    ss = fmaf(v.x, v.x, ss);
+    ss = fmaf(v.y, v.y, ss);
+    ss = fmaf(v.z, v.z, ss);
+    ss = fmaf(v.w, v.w, ss);
+  }
+  ss = warp_sum(ss);
+  const float nr = sqrtf(ss);
+  const float den = fmaxf(nr, 1e-12f);
+  if (lane == 0) norm[row] = nr;
+  float *hr = h + row * d;
+  for (int64_t c = lane * 4; c < d; c += 128) {
+    const float4 v = ldg_f4(xr + c);
+    *reinterpret_cast<float4 *>(hr + c) = make_float4(v.x / den, v.y / den, v.z / den, v.w / den);
+  }
+}
+
+// gx = (gh - h <h,gh>) / max(norm, eps)     (norm > eps case of torch's normalize backward;
+// for norm <= eps torch gives gh/eps, reproduced below)
+__global__ void __launch_bounds__(256)
+row_normalize_bwd_kernel(const float *__restrict__ gh, const float *__restrict__ h,
+                         const float *__restrict__ norm, int64_t n, int64_t d, float *__restrict__ gx) {
+  const int lane = threadIdx.x & 31;
+  const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (row >= n) return;
+  const float *gr = gh + row * d, *hr = h + row * d;
+  float dot = 0.f;
+  for (int64_t c = lane * 4; c < d; c += 128) {
+    const float4 a = ldg_f4(gr + c), b = ldg_f4(hr + c);
+    dot = fmaf(a.x, b.x, dot);
+    dot = fmaf(a.y, b.y, dot);
+    dot = fmaf(a.z, b.z, dot);
+    dot = fmaf(a.w, b.w, dot);
+  }
+  dot = warp_sum(dot);
+  const float nr = norm[row];
+  const bool clamped = nr <= 1e-12f;
+  const float inv = 1.f / fmaxf(nr, 1e-12f);
+  if (clamped) dot = 0.f;
+  float *o = gx + row * d;
+  for (int64_t c = lane * 4; c < d; c += 128) {
+    const float4 a = ldg_f4(gr + c), b = ldg_f4(hr + c);
+    *reinterpret_cast<float4 *>(o + c) = make_float4((a.x - b.x * dot) * inv, (a.y - b.y * dot) * inv,
+                                                     (a.z - b.z * dot) * inv, (a.w - b.w * dot) * inv);
+  }
+}
+
+// gZ = scale * gXnext * ELU'(Z) (+ gres)
+__global__ void __launch_bounds__(256)
+elu_bwd_kernel(const float *__restrict__ gxn, const float *__restrict__ z, const float *__restrict__ gres,
+               float scale, int64_t count4, float *__restrict__ gz) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count4) return;
+  const float4 g = ldg_f4(gxn + i * 4), zz = ldg_f4(z + i * 4);
+  float4 o;
+  o.x = scale * g.x * (zz.x > 0.f ? 1.f : expf(zz.x));
+  o.y = scale * g.y * (zz.y > 0.f ? 1.f : expf(zz.y));
+  o.z = scale * g.z * (zz.z > 0.f ? 1.f : expf(zz.z));
+  o.w = scale * g.w * (zz.w > 0.f ? 1.f : expf(zz.w));
+  if (gres) {
+    const float4 r = ldg_f4(gres + i * 4);
+    o.x += r.x;
+    o.y += r.y;
+    o.z += r.z;
+    o.w += r.w;
+  }
+  *reinterpret_cast<float4 *>(gz + i * 4) = o;
+}
+
+// split-K partial reduce: out[i] (+)= sum_z part[z][i], fixed order (deterministic)
+__global__ void __launch_bounds__(256)
+splitk_reduce_kernel(const float *__restrict__ part, int splits, int64_t count, int accumulate,
+                     float *__restrict__ out) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  float s = 0.f;
+  for (int z = 0; z < splits; ++z) s += part[(int64_t)z * count + i];
+  out[i] = accumulate ? out[i] + s : s;
+}
+
+// column sums of G[n,d] -> partial[blocks][d]; each block owns a row slab
+constexpr int CS_ROWS = 256;
+__global__ void __launch_bounds__(256)
+colsum_partial_kernel(const float *__restrict__ g, int64_t n, int64_t d, float *__restrict__ part) {
+  const int64_t r0 = (int64_t)blockIdx.x * CS_ROWS;
+  const int64_t r1 = min(n, r0 + CS_ROWS);
+  for (int64_t c = threadIdx.x; c < d; c += blockDim.x) {
+    float s = 0.f;
+    for (int64_t r = r0; r < r1; ++r) s += g[r * d + c];
+    part[(int64_t)blockIdx.x * d + c] = s;
+  }
+}
+
+static int splits_for(int64_t n) {
+  // dW is d x d (a handful of tiles): split the node dimension so that ~2 waves of CTAs exist
+  int64_t s = ceil_div<int64_t>(n, 512);
+  if (s < 1) s = 1;
+  if (s > 2 * kNumSMs) s = 2 * kNumSMs;
+  return (int)s;
+}
+
+}  // namespace gdr
+
+using namespace gdr;
+
+extern "C" {
+
+int gdr_gcn_layer_fwd_f32(const float *p, const float *t, const float *w1, const float *b1, const float *w2,
+                          const float *b2, const float *residual, float decay, int64_t n, int64_t d,
+                          float *z_out, float *xnext_out, gdr_stream_t stream) {
+  GDR_CHECK_ARG(n >= 0 && d > 0, GDR_E_BADARG, "gcn_layer_fwd: bad sizes");
+  GDR_CHECK_ARG(d % 4 == 0, GDR_E_SHAPE, "gcn_layer_fwd: d=%lld must be a multiple of 4", (long long)d);
+  GDR_CHECK_ARG(p && t && w1 && b1 && w2 && b2 && z_out && xnext_out, GDR_E_BADARG, "gcn_layer_fwd: null pointer");
+  if (n == 0) return GDR_OK;
+  GemmParams g{};
+  g.a[0] = p; g.b[0] = w1; g.lda[0] = d; g.ldb[0] = d; g.kseg[0] = d;
+  g.a[1] = t; g.b[1] = w2; g.lda[1] = d; g.ldb[1] = d; g.kseg[1] = d;
+  g.nseg = 2;
+  g.m = n; g.n = d;
+  g.c = z_out; g.ldc = d;
+  g.bias1 = b1; g.bias2 = b2; g.residual = residual; g.decay = decay; g.xnext = xnext_out;
+  dim3 grid((unsigned)ceil_div<int64_t>(d, GBN), (unsigned)ceil_div<int64_t>(n, GBM), 1);
+  gemm_f32_kernel<true, true, EPI_LAYER><<<grid, GTHREADS, 0, as_stream(stream)>>>(g);
+  GDR_LAUNCHED();
+  return GDR_OK;
+}
+
+int gdr_row_normalize_fwd_f32(const float *x, int64_t n, int64_t d, float *h_out, float *norm_out,
+                              gdr_stream_t stream) {
+  GDR_CHECK_ARG(n >= 0 && d > 0 && x && h_out && norm_out, GDR_E_BADARG, "row_normalize_fwd: bad args");
+  GDR_CHECK_ARG(d % 4 == 0, GDR_E_SHAPE, "row_normalize_fwd: d must be a multiple of 4");
+  if (n == 0) return GDR_OK;
+  row_normalize_fwd_kernel<<<(unsigned)ceil_div<int64_t>(n * 32, 256), 256, 0, as_stream(stream)>>>(x, n, d, h_out,
+                                                                                                   norm_out);
+  GDR_LAUNCHED();
+  return GDR_OK;
+}
+
+int gdr_row_normalize_bwd_f32(const float *gh, const float *h, const float *norm, int64_t n, int64_t d,
+                              float *gx_out, gdr_stream_t stream) {
+  GDR_CHECK_ARG(n >= 0 && d > 0 && gh && h && norm && gx_out, GDR_E_BADARG, "row_normalize_bwd: bad args");
+  GDR_CHECK_ARG(d % 4 == 0, GDR_E_SHAPE, "row_normalize_bwd: d must be a multiple of 4");
+  if (n == 0) return GDR_OK;
+  row_normalize_bwd_kernel<<<(unsigned)ceil_div<int64_t>(n * 32, 256), 256, 0, as_stream(stream)>>>(gh, h, norm, n, d,
+                                                                                                   gx_out);
+  GDR_LAUNCHED();
+  return GDR_OK;
+}
+
+int gdr_elu_bwd_f32(const float *gxnext, const float *z, const float *gres, float scale, int64_t count,
+                    float *gz_out, gdr_stream_t stream) {
+  GDR_CHECK_ARG(count >= 0 && gxnext && z && gz_out, GDR_E_BADARG, "elu_bwd: bad args");
+  GDR_CHECK_ARG(count % 4 == 0, GDR_E_SHAPE, "elu_bwd: count must be a multiple of 4");
+  if (count == 0) return GDR_OK;
+  elu_bwd_kernel<<<(unsigned)ceil_div<int64_t>(count / 4, 256), 256, 0, as_stream(stream)>>>(gxnext, z, gres, scale,
+                                                                                            count / 4, gz_out);
+  GDR_LAUNCHED();
+  return GDR_OK;
+}
+
+int gdr_linear_bwd_input_f32(const float *g, const float *w, const float *e1, const float *e2, int64_t n,
+                             int64_t d, float *c_out, gdr_stream_t stream) {
+  GDR_CHECK_ARG(n >= 0 && d > 0 && g && w && c_out, GDR_E_BADARG, "linear_bwd_input: bad args");
+  GDR_CHECK_ARG(d % 4 == 0, GDR_E_SHAPE, "linear_bwd_input: d must be a multiple of 4");
+  GDR_CHECK_ARG((e1 == nullptr) == (e2 == nullptr), GDR_E_BADARG, "linear_bwd_input: e1/e2 must come together");
+  if (n == 0) return GDR_OK;
+  GemmParams q{};
+  q.a[0] = g; q.lda[0] = d;   // A(m=node, k=out) = G[m*d + k]        (K-major)
+  q.b[0] = w; q.ldb[0] = d;   // B(n=in,  k=out) = W[k*d + n]         (not K-major)
+  q.kseg[0] = d; q.nseg = 1;
+  q.m = n; q.n = d; q.c = c_out; q.ldc = d; q.e1 = e1; q.e2 = e2;
+  dim3 grid((unsigned)ceil_div<int64_t>(d, GBN), (unsigned)ceil_div<int64_t>(n, GBM), 1);
+  gemm_f32_kernel<true, false, EPI_STORE><<<grid, GTHREADS, 0, as_stream(stream)>>>(q);
+  GDR_LAUNCHED();
+  return GDR_OK;
+}
+
+int64_t gdr_linear_bwd_weight_workspace_bytes(int64_t n, int64_t d) {
+  if (n < 0 || d <= 0) return GDR_E_BADARG;
+  const int64_t splits = splits_for(n);
+  const int64_t cs_blocks = ceil_div<int64_t>(n > 0 ? n : 1, CS_ROWS);
+  return align_up(splits * d * d * 4, 256) + align_up(cs_blocks * d * 4, 256) + 512;
+}
+
+int gdr_linear_bwd_weight_f32(const float *g, const float *a, int64_t n, int64_t d, int accumulate, float *dw,
+                              float *db, void *workspace, int64_t workspace_bytes, gdr_stream_t stream) {
+  GDR_CHECK_ARG(n >= 0 && d > 0 && g && a && dw && workspace, GDR_E_BADARG, "linear_bwd_weight: bad args");
+  GDR_CHECK_ARG(d % 4 == 0, GDR_E_SHAPE, "linear_bwd_weight: d must be a multiple of 4");
+  GDR_CHECK_ARG(workspace_bytes >= gdr_linear_bwd_weight_workspace_bytes(n, d), GDR_E_WORKSPACE,
+                "linear_bwd_weight: workspace too small");
+  cudaStream_t st = as_stream(stream);
+  const int splits = splits_for(n);
+  Carver cv(workspace);
+  float *part = cv.take<float>((int64_t)splits * d * d);
+  const int64_t cs_blocks = ceil_div<int64_t>(n > 0 ? n : 1, CS_ROWS);
+  float *cpart = cv.take<float>(cs_blocks * d);
+  if (n == 0) {
+    if (!accumulate) {
+      GDR_CUDA(cudaMemsetAsync(dw, 0, d * d * 4, st));
+      if (db) GDR_CUDA(cudaMemsetAsync(db, 0, d * 4, st));
+    }
+    return GDR_OK;
+  }
+  GemmParams q{};
+  q.a[0] = g; q.lda[0] = d;  // A(m=out, k=node) = G[k*d + m]
+  q.b[0] = a; q.ldb[0] = d;  // B(n=in,  k=node) = A[k*d + n]
+  q.kseg[0] = n; q.nseg = 1;
+  q.m = d; q.n = d; q.c = part; q.ldc = d;
+  q.k_per_split = ceil_div<int64_t>(ceil_div<int64_t>(n, splits), GBK) * GBK;
+  dim3 grid((unsigned)ceil_div<int64_t>(d, GBN), (unsigned)ceil_div<int64_t>(d, GBM), (unsigned)splits);
+  gemm_f32_kernel<false, false, EPI_SPLITK><<<grid, GTHREADS, 0, st>>>(q);
+  GDR_LAUNCHED();
+  splitk_reduce_kernel<<<(unsigned)ceil_div<int64_t>(d * d, 256), 256, 0, st>>>(part, splits, d * d, accumulate, dw);
+  GDR_LAUNCHED();
+  if (db) {
+    colsum_partial_kernel<<<(unsigned)cs_blocks, 256, 0, st>>>(g, n, d, cpart);
+    GDR_LAUNCHED();
+    splitk_reduce_kernel<<<(unsigned)ceil_div<int64_t>(d, 256), 256, 0, st>>>(cpart, (int)cs_blocks, d, accumulate,
+                                                                             db);
+    GDR_LAUNCHED();
+  }
+  return GDR_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,161 @@
+// loss.cu — GSS similarity-separation loss (modules/model.py:214-221), its gradient, the
+// batch gather/scatter around it, and the Adam step (train.py:139,184).
+//
+//   E = embs[index] ; G = E·Eᵀ ; loss = mean(-0.5*alpha*(relu(G)-beta)^2)
+//   dLoss/dG = -alpha*(relu(G)-beta)*[G>0] / B^2 ;  dLoss/dE = (dG + dGᵀ)·E = 2·dG·E  (G symmetric)
+//
+// Forward and gradient come out of one call: the Gram GEMM's epilogue turns each G tile
+// into (loss partial, 2·dG tile) in registers, a second GEMM contracts 2·dG with E.
+#include "gemm_simt.cuh"
+
+namespace gdr {
+
+__global__ void __launch_bounds__(256)
+gather_rows_kernel(const float *__restrict__ src, const int64_t *__restrict__ index, int64_t b, int64_t n,
+                   int64_t d, float *__restrict__ dst) {
+  const int lane = threadIdx.x & 31;
+  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (i >= b) return;
+  int64_t r = index ? index[i] : i;
+  if (r < 0) r += n;  // torch-style negative indices
+  const float *s = src + r * d;
+  float *o = dst + i * d;
+  for (int64_t c = lane * 4; c < d; c += 128) *reinterpret_cast<float4 *>(o + c) = ldg_f4(s + c);
+}
+
+__global__ void __launch_bounds__(256)
+scatter_rows_kernel(const float *__restrict__ ge, const int64_t *__restrict__ index, int64_t b, int64_t n,
+                    int64_t d, const float *__restrict__ scale_dev, float *__restrict__ gh) {
+  const int lane = threadIdx.x & 31;
+  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (i >= b) return;
+  const float sc = scale_dev ? __ldg(scale_dev) : 1.f;
+  int64_t r = index ? index[i] : i;
+  if (r < 0) r += n;
+  const float *s = ge + i * d;
+  float *o = gh + r * d;
+  // atomics: duplicate indices in a user-supplied batch must accumulate (index_put_ accumulate=True)
+  for (int64_t c = lane; c < d; c += 32) atomicAdd(o + c, sc * s[c]);
+}
+
+__global__ void loss_finalize_kernel(const double *__restrict__ partials, int count, double inv_count,
+                                     float *__restrict__ loss_out) {
+  __shared__ double red[32];
+  double s = 0.0;
+  for (int i = threadIdx.x; i < count; i += blockDim.x) s += partials[i];
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double tot = 0.0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) tot += red[w];
+    *loss_out = (float)(tot * inv_count);
+  }
+}
+
+// torch.optim.Adam (amsgrad=False, weight_decay=0, maximize=False), single-tensor formulas:
+//   m = lerp(m, g, 1-b1) ; v = b2*v + (1-b2)*g*g ; denom = sqrt(v)/sqrt(1-b2^t) + eps
+//   p -= (lr/(1-b1^t)) * m/denom
+__global__ void __launch_bounds__(256)
+adam_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restrict__ m, float *__restrict__ v,
+            int64_t count, float lr, float b1, float b2, float eps, const int32_t *__restrict__ step_dev) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= count) return;
+  const int step = *step_dev + 1;
+  const double bc1 = 1.0 - pow((double)b1, (double)step);
+  const double bc2 = 1.0 - pow((double)b2, (double)step);
+  const float step_size = (float)((double)lr / bc1);
+  const float bc2_sqrt = (float)sqrt(bc2);
+  const float gi = g[i];
+  float mi = m[i], vi = v[i];
+  mi = mi + (gi - mi) * (1.f - b1);
+  vi = vi * b2 + (1.f - b2) * gi * gi;
+  m[i] = mi;
+  v[i] = vi;
+  const float denom = sqrtf(vi) / bc2_sqrt + eps;
+  p[i] = p[i] - step_size * (mi / denom);
+}
+
+__global__ void bump_step_kernel(int32_t *step_dev) { *step_dev += 1; }
+
+}  // namespace gdr
+
+using namespace gdr;
+
+extern "C" {
+
+int64_t gdr_gss_loss_workspace_bytes(int64_t b, int64_t d) {
+  if (b < 0 || d <= 0) return GDR_E_BADARG;
+  const int64_t ldw = align_up(b, 4);
+  const int64_t tiles = ceil_div<int64_t>(b > 0 ? b : 1, GBM);
+  return align_up(b * d * 4, 256) + align_up(b * ldw * 4, 256) + align_up(tiles * tiles * 8, 256) + 1024;
+}
+
+int gdr_gss_loss_fwd_bwd_f32(const float *embs, const int64_t *index, int64_t b, int64_t n, int64_t d, float alpha,
+                             float beta, float *loss_out, float *grad_e_out, void *workspace,
+                             int64_t workspace_bytes, gdr_stream_t stream) {
+  GDR_CHECK_ARG(b > 0 && n > 0 && d > 0, GDR_E_BADARG, "gss_loss: bad sizes");
+  GDR_CHECK_ARG(d % 4 == 0, GDR_E_SHAPE, "gss_loss: d must be a multiple of 4");
+  GDR_CHECK_ARG(embs && loss_out && grad_e_out && workspace, GDR_E_BADARG, "gss_loss: null pointer");
+  GDR_CHECK_ARG(workspace_bytes >= gdr_gss_loss_workspace_bytes(b, d), GDR_E_WORKSPACE,
+                "gss_loss: workspace too small (B=%lld needs a BxB tile buffer)", (long long)b);
+  cudaStream_t st = as_stream(stream);
+  const int64_t ldw = align_up(b, 4);
+  const int64_t tiles = ceil_div<int64_t>(b, GBM);
+  Carver cv(workspace);
+  float *e = cv.take<float>(b * d);
+  float *wm = cv.take<float>(b * ldw);
+  double *partials = cv.take<double>(tiles * tiles);
+
+  gather_rows_kernel<<<(unsigned)ceil_div<int64_t>(b * 32, 256), 256, 0, st>>>(embs, index, b, n, d, e);
+  GDR_LAUNCHED();
+
+  GemmParams g{};
+  g.a[0] = e; g.lda[0] = d; g.b[0] = e; g.ldb[0] = d; g.kseg[0] = d; g.nseg = 1;
+  g.m = b; g.n = b; g.c = wm; g.ldc = ldw;
+  g.alpha = alpha; g.beta = beta;
+  g.wscale = (float)(2.0 / ((double)b * (double)b));
+  g.loss_partials = partials;
+  dim3 grid((unsigned)tiles, (unsigned)tiles, 1);
+  gemm_f32_kernel<true, true, EPI_GSS><<<grid, GTHREADS, 0, st>>>(g);
+  GDR_LAUNCHED();
+
+  loss_finalize_kernel<<<1, 256, 0, st>>>(partials, (int)(tiles * tiles), 1.0 / ((double)b * (double)b), loss_out);
+  GDR_LAUNCHED();
+
+  GemmParams q{};
+  q.a[0] = wm; q.lda[0] = ldw;  // A(m=i, k=j) = Wm[i*ldw + j]
+  q.b[0] = e; q.ldb[0] = d;     // B(n=c, k=j) = E[j*d + c]
+  q.kseg[0] = b; q.nseg = 1;
+  q.m = b; q.n = d; q.c = grad_e_out; q.ldc = d;
+  dim3 grid2((unsigned)ceil_div<int64_t>(d, GBN), (unsigned)tiles, 1);
+  gemm_f32_kernel<true, false, EPI_STORE><<<grid2, GTHREADS, 0, st>>>(q);
+  GDR_LAUNCHED();
+  return GDR_OK;
+}
+
+int gdr_scatter_rows_f32(const float *ge, const int64_t *index, int64_t b, int64_t n, int64_t d,
+                         const float *scale_dev, float *gh, gdr_stream_t stream) {
+  GDR_CHECK_ARG(b >= 0 && d > 0 && ge && gh, GDR_E_BADARG, "scatter_rows: bad args");
+  if (b == 0) return GDR_OK;
+  scatter_rows_kernel<<<(unsigned)ceil_div<int64_t>(b * 32, 256), 256, 0, as_stream(stream)>>>(
+      ge, index, b, n, d, scale_dev, gh);
+  GDR_LAUNCHED();
+  return GDR_OK;
+}
+
+int gdr_adam_step_f32(float *param, const float *grad, float *exp_avg, float *exp_avg_sq, int64_t count, float lr,
+                      float beta1, float beta2, float eps, int32_t *step_dev, gdr_stream_t stream) {
+  GDR_CHECK_ARG(count >= 0 && param && grad && exp_avg && exp_avg_sq && step_dev, GDR_E_BADARG,
+                "adam_step: bad args");
+  if (count == 0) return GDR_OK;
+  cudaStream_t st = as_stream(stream);
+  adam_kernel<<<(unsigned)ceil_div<int64_t>(count, 256), 256, 0, st>>>(param, grad, exp_avg, exp_avg_sq, count, lr,
+                                                                      beta1, beta2, eps, step_dev);
+  GDR_LAUNCHED();
+  bump_step_kernel<<<1, 1, 0, st>>>(step_dev);
+  GDR_LAUNCHED();
+  return GDR_OK;
+}
+
+}  // extern "C"

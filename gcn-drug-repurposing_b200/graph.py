@@ -1,0 +1,181 @@
+"""DeviceCSR — the adjacency as the kernels want it: int32 rowptr/col + values in HBM, plus a
+lazily built transposed copy for the backward pass (Âᵀ·G).
+
+The reference hands the model an *uncoalesced int64 COO* torch sparse tensor
+(helpers/helper.py:92-96, consumed by torch.sparse.mm at modules/model.py:163,169).  The
+drop-in layer converts it once on the device (gdr_csr_from_coo) and caches the result on the
+adjacency tensor object, which train.py passes unchanged every iteration (train.py:161).
+The transpose is always explicit: Â is not assumed symmetric.
+"""
+import ctypes
+
+import numpy as np
+import torch
+
+from . import _ffi
+
+
+class DeviceCSR:
+    def __init__(self, rowptr, col, val, n_rows, n_cols):
+        self.rowptr = rowptr  # int32 [n_rows+1]
+        self.col = col        # int32 [nnz]
+        self.val = val        # float32 / float64 [nnz]
+        self.n_rows = int(n_rows)
+        self.n_cols = int(n_cols)
+        self._t = None
+
+    # ---- constructors -------------------------------------------------------------------
+    @classmethod
+    def from_coo(cls, row, col, val, n_rows, n_cols):
+        """row/col: int64 CUDA tensors (any order, duplicates kept); val: fp32/fp64 CUDA tensor."""
+        L = _ffi.lib()
+        dev = row.device
+        nnz = int(row.numel())
+        row = row.contiguous()
+        col = col.contiguous()
+        val = val.contiguous()
+        rowptr = torch.empty(n_rows + 1, dtype=torch.int32, device=dev)
+        colo = torch.empty(max(nnz, 1), dtype=torch.int32, device=dev)[:nnz]
+        perm = torch.empty(max(nnz, 1), dtype=torch.int64, device=dev)[:nnz]
+        ws_bytes = L.gdr_csr_from_coo_workspace_bytes(nnz, n_rows, n_cols)
+        ws = _ffi.workspace(ws_bytes, dev)
+        _ffi.check(L.gdr_csr_from_coo(_ffi.ptr(row), _ffi.ptr(col), nnz, n_rows, n_cols, _ffi.ptr(rowptr),
+                                      _ffi.ptr(colo), _ffi.ptr(perm), _ffi.ptr(ws), ws.numel(), _ffi.stream()),
+                   "csr_from_coo")
+        valo = torch.empty_like(val)
+        _ffi.check(L.gdr_permute_values(_ffi.ptr(val), _ffi.ptr(perm), nnz, val.element_size(), _ffi.ptr(valo),
+                                        _ffi.stream()), "permute_values")
+        return cls(rowptr, colo, valo, n_rows, n_cols)
+
+    @classmethod
+    def from_torch_sparse(cls, adj):
+        """adj: torch sparse COO tensor on a CUDA device (what convert_sparse_matrix_to_sparse_tensor
+        returns, moved with .cuda() as train.py:120 does)."""
+        if not adj.is_cuda:
+            raise RuntimeError("DeviceCSR: the adjacency must live on a CUDA device (no CPU path)")
+        if adj.layout != torch.sparse_coo:
+            raise RuntimeError(f"DeviceCSR: expected a sparse COO adjacency, got {adj.layout}")
+        idx = adj._indices()
+        return cls.from_coo(idx[0], idx[1], adj._values(), adj.shape[0], adj.shape[1])
+
+    @classmethod
+    def from_scipy(cls, m, device, dtype=torch.float32):
+        """m: scipy csr_matrix (indices need not be sorted: goes through the COO path)."""
+        m = m.tocsr()
+        if m.has_sorted_indices and m.has_canonical_format:
+            rowptr = torch.from_numpy(np.asarray(m.indptr, dtype=np.int32)).to(device)
+            col = torch.from_numpy(np.asarray(m.indices, dtype=np.int32)).to(device)
+            val = torch.from_numpy(np.asarray(m.data)).to(device=device, dtype=dtype)
+            return cls(rowptr, col, val, m.shape[0], m.shape[1])
+        coo = m.tocoo()
+        return cls.from_coo(torch.from_numpy(coo.row.astype(np.int64)).to(device),
+                            torch.from_numpy(coo.col.astype(np.int64)).to(device),
+                            torch.from_numpy(coo.data).to(device=device, dtype=dtype), m.shape[0], m.shape[1])
+
+    # ---- properties ------------------------------------------------------------------------
+    @property
+    def nnz(self):
+        return int(self.col.numel())
+
+    @property
+    def device(self):
+        return self.rowptr.device
+
+    def to_scipy(self):
+        import scipy.sparse as sp
+        return sp.csr_matrix((self.val.cpu().numpy(), self.col.cpu().numpy(), self.rowptr.cpu().numpy()),
+                             shape=(self.n_rows, self.n_cols))
+
+    # ---- transpose ----------------------------------------------------------------------------
+    def transpose(self):
+        if self._t is None:
+            L = _ffi.lib()
+            dev = self.device
+            nnz = self.nnz
+            t_rowptr = torch.empty(self.n_cols + 1, dtype=torch.int32, device=dev)
+            t_col = torch.empty(max(nnz, 1), dtype=torch.int32, device=dev)[:nnz]
+            perm = torch.empty(max(nnz, 1), dtype=torch.int64, device=dev)[:nnz]
+            ws = _ffi.workspace(L.gdr_csr_transpose_workspace_bytes(nnz, self.n_rows, self.n_cols), dev)
+            _ffi.check(L.gdr_csr_transpose(_ffi.ptr(self.rowptr), _ffi.ptr(self.col), nnz, self.n_rows, self.n_cols,
+                                           _ffi.ptr(t_rowptr), _ffi.ptr(t_col), _ffi.ptr(perm), _ffi.ptr(ws),
+                                           ws.numel(), _ffi.stream()), "csr_transpose")
+            t_val = torch.empty_like(self.val)
+            _ffi.check(L.gdr_permute_values(_ffi.ptr(self.val), _ffi.ptr(perm), nnz, self.val.element_size(),
+                                            _ffi.ptr(t_val), _ffi.stream()), "permute_values")
+            self._t = DeviceCSR(t_rowptr, t_col, t_val, self.n_cols, self.n_rows)
+            self._t._t = self
+        return self._t
+
+    # ---- (A + I) symmetric normalisation: preprocess_graph on the device -----------------------
+    def normalized_with_identity(self):
+        """D^-1/2 (A+I) D^-1/2 in fp64 (helpers/helper.py:82-89).  Returns a new fp64 DeviceCSR."""
+        if self.n_rows != self.n_cols:
+            raise RuntimeError("preprocess_graph needs a square adjacency")
+        if self.val.dtype != torch.float64:
+            raise RuntimeError("preprocess_graph runs in fp64 like the reference (got %s)" % self.val.dtype)
+        L = _ffi.lib()
+        dev = self.device
+        n = self.n_rows
+        out_rowptr = torch.empty(n + 1, dtype=torch.int32, device=dev)
+        ws = _ffi.workspace(L.gdr_csr_add_identity_workspace_bytes(n), dev)
+        nnz_out = ctypes.c_int64(0)
+        _ffi.check(L.gdr_csr_add_identity_count(_ffi.ptr(self.rowptr), _ffi.ptr(self.col), n, _ffi.ptr(out_rowptr),
+                                                ctypes.byref(nnz_out), _ffi.ptr(ws), ws.numel(), _ffi.stream()),
+                   "csr_add_identity_count")
+        nnz = int(nnz_out.value)
+        out_col = torch.empty(max(nnz, 1), dtype=torch.int32, device=dev)[:nnz]
+        out_val = torch.empty(max(nnz, 1), dtype=torch.float64, device=dev)[:nnz]
+        dis = torch.empty(max(n, 1), dtype=torch.float64, device=dev)[:n]
+        _ffi.check(L.gdr_csr_normalize_f64(_ffi.ptr(self.rowptr), _ffi.ptr(self.col), _ffi.ptr(self.val), n,
+                                           _ffi.ptr(out_rowptr), _ffi.ptr(out_col), _ffi.ptr(out_val),
+                                           _ffi.ptr(dis), _ffi.stream()), "csr_normalize")
+        out = DeviceCSR(out_rowptr, out_col, out_val, n, n)
+        out.deg_inv_sqrt = dis
+        return out
+
+    def astype(self, dtype):
+        if self.val.dtype == dtype:
+            return self
+        return DeviceCSR(self.rowptr, self.col, self.val.to(dtype), self.n_rows, self.n_cols)
+
+    # ---- SpMM ------------------------------------------------------------------------------------
+    def spmm(self, x, mul=None, e1=None, e2=None, out=None):
+        """out = self · x  (gathered operand x ⊙ mul if mul is given; + e1 ⊙ e2 if given)."""
+        L = _ffi.lib()
+        if x.dim() != 2 or x.shape[0] != self.n_cols:
+            raise RuntimeError(f"spmm: x has shape {tuple(x.shape)}, adjacency is {self.n_rows}x{self.n_cols}")
+        if x.dtype != self.val.dtype:
+            raise RuntimeError(f"spmm: dtype mismatch ({x.dtype} features, {self.val.dtype} adjacency)")
+        d = x.shape[1]
+        if out is None:
+            out = torch.empty(self.n_rows, d, dtype=x.dtype, device=x.device)
+        if x.dtype == torch.float32:
+            _ffi.check(L.gdr_spmm_csr_f32(_ffi.ptr(self.rowptr), _ffi.ptr(self.col), _ffi.ptr(self.val), self.n_rows,
+                                          d, _ffi.ptr(x), _ffi.ptr(mul), _ffi.ptr(e1), _ffi.ptr(e2), _ffi.ptr(out),
+                                          _ffi.stream()), "spmm_csr_f32")
+        elif x.dtype == torch.float64:
+            if mul is not None or e1 is not None:
+                raise RuntimeError("spmm: fused operands are fp32-only")
+            _ffi.check(L.gdr_spmm_csr_f64(_ffi.ptr(self.rowptr), _ffi.ptr(self.col), _ffi.ptr(self.val), self.n_rows,
+                                          d, _ffi.ptr(x), _ffi.ptr(out), _ffi.stream()), "spmm_csr_f64")
+        else:
+            raise RuntimeError(f"spmm: unsupported dtype {x.dtype}")
+        return out
+
+
+def device_csr_of(adj):
+    """DeviceCSR for the adjacency object the reference API passes around, built once and cached
+    on the object (train.py passes the same tensor every iteration)."""
+    if isinstance(adj, DeviceCSR):
+        return adj
+    cached = getattr(adj, "_gdr_csr", None)
+    if cached is not None:
+        return cached
+    if not isinstance(adj, torch.Tensor):
+        raise RuntimeError(f"adjacency must be a torch sparse tensor or DeviceCSR, got {type(adj)}")
+    csr = DeviceCSR.from_torch_sparse(adj)
+    try:
+        adj._gdr_csr = csr
+    except Exception:
+        pass
+    return csr

@@ -1,0 +1,197 @@
+/*
+ * gdr.h — C ABI of libgdr.so: the B200 (sm_100a) propagation path of
+ * bowang-lab/gcn-drug-repurposing.
+ *
+ * The reference has no FFI: its "operator API" is a set of Python call sites that
+ * end in torch / numpy / scipy library calls.  Every entry point below replaces one
+ * of those library calls (cited as reference file:line).  The host-side mirror of the
+ * reference classes (package `gcn-drug-repurposing_b200`) binds these with ctypes.
+ *
+ * Conventions
+ *   - plain C types only: device pointers, int64 sizes, a cudaStream_t passed as void*.
+ *   - every pointer is a DEVICE pointer unless the name ends in `_host`.
+ *   - the caller owns every buffer, including workspaces (sizes from *_workspace_bytes).
+ *   - return value: 0 = ok, >0 = cudaError_t, <0 = argument error (GDR_E_*).
+ *     gdr_last_error_string() gives the text of the last failure on this thread.
+ *   - all kernels are stream-ordered on `stream`; nothing synchronises the device
+ *     unless the entry point's comment says so.
+ *   - feature matrices are dense row-major, row stride == d (number of columns),
+ *     d % 4 == 0 and 16-byte aligned base pointers.
+ *   - CSR: int32 rowptr[n_rows+1], int32 col[nnz], values fp32 or fp64.
+ */
+#ifndef GDR_H_
+#define GDR_H_
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define GDR_OK 0
+#define GDR_E_BADARG (-1)   /* null pointer, negative size */
+#define GDR_E_SHAPE (-2)    /* unsupported width / alignment */
+#define GDR_E_WORKSPACE (-3) /* workspace too small */
+#define GDR_E_NOCONV (-4)   /* power iteration hit max_iter (reference raises, diffusion_profiles.py:90) */
+
+typedef void *gdr_stream_t; /* cudaStream_t */
+
+/* ---- library ------------------------------------------------------------------ */
+int gdr_version(void);
+const char *gdr_last_error_string(void);
+/* number of kernels this library has launched in this process (bench "gpu_launches") */
+int64_t gdr_launch_count(void);
+void gdr_launch_count_reset(void);
+
+/* ---- CSR construction ----------------------------------------------------------- *
+ * replaces scipy's csr/coo conversions around helpers/helper.py:53,89,92-96 and the
+ * torch sparse COO the model receives (modules/model.py:163).                        */
+
+/* COO (int64 row/col as torch gives them, any order, duplicates kept) -> CSR sorted by
+ * (row, col), stable.  perm_out (optional, int64[nnz]) receives the source position of
+ * every CSR entry so that values in another dtype can be permuted by the caller.     */
+int64_t gdr_csr_from_coo_workspace_bytes(int64_t nnz, int64_t n_rows, int64_t n_cols);
+int gdr_csr_from_coo(const int64_t *coo_row, const int64_t *coo_col, int64_t nnz,
+                     int64_t n_rows, int64_t n_cols, int32_t *rowptr_out,
+                     int32_t *col_out, int64_t *perm_out, void *workspace,
+                     int64_t workspace_bytes, gdr_stream_t stream);
+/* values_out[i] = values_in[perm[i]] (elem_bytes 4 or 8) */
+int gdr_permute_values(const void *values_in, const int64_t *perm, int64_t nnz,
+                       int elem_bytes, void *values_out, gdr_stream_t stream);
+
+/* CSR -> CSR of the transpose, entries of every transposed row ordered by source row
+ * (stable), i.e. exactly scipy's A.T.tocsr().  perm_out as above.                    */
+int64_t gdr_csr_transpose_workspace_bytes(int64_t nnz, int64_t n_rows, int64_t n_cols);
+int gdr_csr_transpose(const int32_t *rowptr, const int32_t *col, int64_t nnz,
+                      int64_t n_rows, int64_t n_cols, int32_t *t_rowptr_out,
+                      int32_t *t_col_out, int64_t *perm_out, void *workspace,
+                      int64_t workspace_bytes, gdr_stream_t stream);
+
+/* preprocess_graph (helpers/helper.py:82-89):  Â = D^-1/2 (A+I) D^-1/2 in fp64, entry
+ * value (a_ij * d_j) * d_i with d = rowsum(A+I)^-1/2.  Input CSR must have sorted rows.
+ * Output nnz = nnz + (rows without a stored diagonal).  Call the _count entry first
+ * (writes out_rowptr and *nnz_out_host after synchronising the stream).              */
+int gdr_csr_add_identity_count(const int32_t *rowptr, const int32_t *col, int64_t n,
+                               int32_t *out_rowptr, int64_t *nnz_out_host,
+                               void *workspace, int64_t workspace_bytes,
+                               gdr_stream_t stream);
+int64_t gdr_csr_add_identity_workspace_bytes(int64_t n);
+int gdr_csr_normalize_f64(const int32_t *rowptr, const int32_t *col, const double *val,
+                          int64_t n, const int32_t *out_rowptr, int32_t *out_col,
+                          double *out_val, double *deg_inv_sqrt_out,
+                          gdr_stream_t stream);
+
+/* ---- SpMM: the aggregation  Y = Â·X  ---------------------------------------------- *
+ * replaces torch.sparse.mm (modules/model.py:163,169), its autograd Âᵀ·G (pass the
+ * transposed CSR) and scipy's x*M (multiscale/diff_prof/diffusion_profiles.py:85).
+ *   Y[r,:] = sum_e val[e] * X[col[e],:] (* P[col[e],:] if mul != NULL)
+ *            (+ E1[r,:] * E2[r,:]       if e1 != NULL)
+ * mul: the reference's torch.mul(Ax, features) (model.py:168) folded into the gather.
+ * e1,e2: the backward's element-wise addend  dX = Âᵀ·dP + dR ⊙ P.                     */
+int gdr_spmm_csr_f32(const int32_t *rowptr, const int32_t *col, const float *val,
+                     int64_t n_rows, int64_t d, const float *x, const float *mul,
+                     const float *e1, const float *e2, float *y, gdr_stream_t stream);
+int gdr_spmm_csr_f64(const int32_t *rowptr, const int32_t *col, const double *val,
+                     int64_t n_rows, int64_t d, const double *x, double *y,
+                     gdr_stream_t stream);
+
+/* ---- dense transform -------------------------------------------------------------- *
+ * GSS_GNNLayer.forward (modules/model.py:163-175) after the two aggregations:
+ *   Z = P·W1ᵀ + b1 + T·W2ᵀ + b2 ;  Y = ELU(Z) ;  Xnext = residual ? residual + decay*Y : Y
+ * (the residual update is ResidualGraphConvolutionalNetwork.forward, model.py:201-203).
+ * W row-major [d_out=d, d_in=d] as nn.Linear stores it.  z_out, xnext_out: [n, d].   */
+int gdr_gcn_layer_fwd_f32(const float *p, const float *t, const float *w1,
+                          const float *b1, const float *w2, const float *b2,
+                          const float *residual, float decay, int64_t n, int64_t d,
+                          float *z_out, float *xnext_out, gdr_stream_t stream);
+
+/* F.normalize(x, dim=1) (model.py:205): h = x / max(||x||_2, 1e-12); norm_out[n]. */
+int gdr_row_normalize_fwd_f32(const float *x, int64_t n, int64_t d, float *h_out,
+                              float *norm_out, gdr_stream_t stream);
+/* backward of the above: gx = (gh - h * <h, gh>) / max(norm, eps).
+ * rows (optional int64[n_rows_sel]) restricts the work to those rows of gh/h (the
+ * batch rows of the loss); gx must then be zero-filled by the caller.               */
+int gdr_row_normalize_bwd_f32(const float *gh, const float *h, const float *norm,
+                              int64_t n, int64_t d, float *gx_out, gdr_stream_t stream);
+
+/* gZ = scale * gXnext * ELU'(Z) (+ gres if not NULL): autograd of F.elu + residual.  */
+int gdr_elu_bwd_f32(const float *gxnext, const float *z, const float *gres, float scale,
+                    int64_t count, float *gz_out, gdr_stream_t stream);
+
+/* C[n,d_in] = G[n,d_out]·W[d_out,d_in] (+ E1 ⊙ E2): autograd of nn.Linear w.r.t. its
+ * input (dP = dZ·W1, dT = dZ·W2), with the dP += dR ⊙ X addend folded in.           */
+int gdr_linear_bwd_input_f32(const float *g, const float *w, const float *e1,
+                             const float *e2, int64_t n, int64_t d, float *c_out,
+                             gdr_stream_t stream);
+
+/* dW[d,d] (+)= Gᵀ·A  and  db[d] (+)= colsum(G): autograd of nn.Linear w.r.t. weight
+ * and bias (dW1 = dZᵀ·P, modules/model.py:165).  accumulate != 0 adds into dw/db.    */
+int64_t gdr_linear_bwd_weight_workspace_bytes(int64_t n, int64_t d);
+int gdr_linear_bwd_weight_f32(const float *g, const float *a, int64_t n, int64_t d,
+                              int accumulate, float *dw, float *db, void *workspace,
+                              int64_t workspace_bytes, gdr_stream_t stream);
+
+/* ---- GSS loss ----------------------------------------------------------------------- *
+ * GSS_loss.gss_loss (modules/model.py:214-221):  E = embs[index]; G = E·Eᵀ;
+ * loss = mean(-0.5*alpha*(relu(G)-beta)^2).  One call gives the loss and dLoss/dE
+ * (B x d, un-scattered); index == NULL means all n rows (B = n).                      */
+int64_t gdr_gss_loss_workspace_bytes(int64_t b, int64_t d);
+int gdr_gss_loss_fwd_bwd_f32(const float *embs, const int64_t *index, int64_t b,
+                             int64_t n, int64_t d, float alpha, float beta,
+                             float *loss_out, float *grad_e_out, void *workspace,
+                             int64_t workspace_bytes, gdr_stream_t stream);
+/* gh[index[i],:] += scale_dev[0] * ge[i,:]  (autograd of embs[index]); gh pre-zeroed. */
+int gdr_scatter_rows_f32(const float *ge, const int64_t *index, int64_t b, int64_t n,
+                         int64_t d, const float *scale_dev, float *gh, gdr_stream_t stream);
+
+/* beta selection (train.py:163-167): np.percentile(flatten(H·Hᵀ), q), linear
+ * interpolation, computed by radix select over recomputed Gram tiles (N×N never
+ * stored).  Synchronises the stream; result to *beta_out_host.                        */
+int64_t gdr_gram_percentile_workspace_bytes(int64_t n, int64_t d);
+int gdr_gram_percentile_f32(const float *h, int64_t n, int64_t d, double q_percent,
+                            float *beta_out_host, void *workspace,
+                            int64_t workspace_bytes, gdr_stream_t stream);
+
+/* ---- kNN graph (gen_graph, helpers/helper.py:39-44) ---------------------------------- *
+ * S = X·Xᵀ in fp64 (x: [n,d] row-major = the reference's X.T) and, per row, the k
+ * largest entries (np.argpartition(S,-k,1)[:,-k:], an unordered set): indices int32
+ * [n,k] sorted by descending similarity, values fp64 [n,k].  N×N is never stored.     */
+int gdr_gram_topk_f64(const double *x, int64_t n, int64_t d, int64_t k,
+                      int32_t *idx_out, double *val_out, gdr_stream_t stream);
+
+/* ---- optimizer ------------------------------------------------------------------------ *
+ * torch.optim.Adam single step (train.py:139,184), one launch for all tensors laid out
+ * back to back in flat buffers of `count` floats; step_dev: device int32 counter that
+ * the kernel increments (so the launch is CUDA-graph replayable).                       */
+int gdr_adam_step_f32(float *param, const float *grad, float *exp_avg, float *exp_avg_sq,
+                      int64_t count, float lr, float beta1, float beta2, float eps,
+                      int32_t *step_dev, gdr_stream_t stream);
+
+/* ---- diffusion profiles (multiscale/diff_prof/diffusion_profiles.py:29-90) ----------- *
+ * Batched personalised-PageRank power iteration for `n_seeds` seeds, each with the
+ * reference's per-seed matrix surgery (all other drugs/indications become sinks; edges
+ * protein->seed removed; rows renormalised).  See gdr_rwr.h-style comment in rwr.cu.
+ *   M   : CSR of the weighted MSI adjacency (rows = sources), fp64.
+ *   Mt  : CSR of its transpose (rows = targets), values permuted accordingly.
+ *   is_sink[n]       : 1 for every drug/indication node.
+ *   seed_node[s]     : node index of seed s.
+ *   rm_ptr[s..s+1], rm_node[] : for seed s the source nodes u whose edge u->seed is
+ *                      deleted (the reference's drug_or_indication2proteins[seed]).
+ *   x_out [n_seeds, n]: diffusion profiles (row s = profile of seed s).
+ *   iters_out[n_seeds]: iteration at which each seed met ||dx||_1 < n*tol.
+ * Synchronises the stream.  Returns GDR_E_NOCONV if any seed hit max_iter.             */
+int64_t gdr_rwr_workspace_bytes(int64_t n, int64_t nnz, int64_t n_seeds,
+                                int64_t n_removed);
+int gdr_rwr_solve_f64(const int32_t *m_rowptr, const int32_t *m_col, const double *m_val,
+                      const int32_t *mt_rowptr, const int32_t *mt_col,
+                      const double *mt_val, int64_t n, int64_t nnz,
+                      const uint8_t *is_sink, const int32_t *seed_node, int64_t n_seeds,
+                      const int32_t *rm_ptr, const int32_t *rm_node, int64_t n_removed,
+                      double alpha, double tol, int64_t max_iter, double *x_out,
+                      int32_t *iters_out, void *workspace, int64_t workspace_bytes,
+                      gdr_stream_t stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GDR_H_ */

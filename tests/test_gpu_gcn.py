@@ -1,0 +1,260 @@
+"""GPU parity tests of the GCN path: the CUDA kernels (through the C ABI, via the drop-in classes)
+against the oracle (oracle/gcn_oracle.py: the reference's own library calls on CPU) and against the
+golden fixtures generated from the reference itself (tests/golden, oracle/gen_golden.py).
+
+Tolerance (north_star): index structures bit-exact; fp32 values <= 1e-5 relative or <= 1e-6 absolute.
+"""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+import torch
+
+from .conftest import assert_close, load_golden
+from oracle import gcn_oracle
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda:0"
+
+
+def random_csr(n_rows, n_cols, density, seed, dtype=np.float64, empty_rows=True):
+    rng = np.random.default_rng(seed)
+    m = sp.random(n_rows, n_cols, density=density, random_state=rng, format="csr", dtype=np.float64)
+    m.data = rng.uniform(0.1, 1.0, size=m.nnz)
+    if empty_rows and n_rows > 8:
+        m = m.tolil()
+        m[3] = 0
+        m[n_rows - 1] = 0
+        m = m.tocsr()
+        m.eliminate_zeros()
+    m.sort_indices()
+    return m.astype(dtype)
+
+
+# ---- CSR construction: bit-exact structures ----------------------------------------------------
+@pytest.mark.parametrize("n_rows,n_cols,density", [(1, 1, 1.0), (37, 53, 0.2), (1000, 1000, 0.01), (5000, 300, 0.05)])
+def test_csr_from_shuffled_coo_matches_scipy(gdr, n_rows, n_cols, density):
+    m = random_csr(n_rows, n_cols, density, seed=n_rows)
+    coo = m.tocoo()
+    perm = np.random.default_rng(0).permutation(coo.nnz)
+    row = torch.from_numpy(coo.row[perm].astype(np.int64)).to(DEV)
+    col = torch.from_numpy(coo.col[perm].astype(np.int64)).to(DEV)
+    val = torch.from_numpy(coo.data[perm]).to(DEV)
+    csr = gdr.DeviceCSR.from_coo(row, col, val, n_rows, n_cols)
+    assert np.array_equal(csr.rowptr.cpu().numpy(), m.indptr)
+    assert np.array_equal(csr.col.cpu().numpy(), m.indices)
+    assert np.array_equal(csr.val.cpu().numpy(), m.data)
+
+
+def test_csr_empty_matrix(gdr):
+    z = torch.zeros(0, dtype=torch.int64, device=DEV)
+    csr = gdr.DeviceCSR.from_coo(z, z, torch.zeros(0, dtype=torch.float32, device=DEV), 5, 7)
+    assert csr.rowptr.cpu().tolist() == [0] * 6 and csr.nnz == 0
+    y = csr.spmm(torch.ones(7, 128, device=DEV))
+    assert torch.count_nonzero(y).item() == 0
+
+
+@pytest.mark.parametrize("n_rows,n_cols,density", [(37, 53, 0.2), (2000, 1500, 0.01)])
+def test_csr_transpose_matches_scipy(gdr, n_rows, n_cols, density):
+    m = random_csr(n_rows, n_cols, density, seed=7)
+    t = gdr.DeviceCSR.from_scipy(m, DEV, dtype=torch.float64).transpose()
+    mt = m.T.tocsr()
+    mt.sort_indices()
+    assert np.array_equal(t.rowptr.cpu().numpy(), mt.indptr)
+    assert np.array_equal(t.col.cpu().numpy(), mt.indices)
+    assert np.array_equal(t.val.cpu().numpy(), mt.data)
+
+
+@pytest.mark.parametrize("case", ["gcn_knn257.npz", "gcn_knn600_l3.npz", "gcn_edge300_d256.npz"])
+def test_preprocess_graph_matches_reference(gdr, case):
+    g = load_golden(case)
+    n = len(g["x_adj_indptr"]) - 1
+    x_adj = sp.csr_matrix((g["x_adj_data"], g["x_adj_indices"], g["x_adj_indptr"]), shape=(n, n))
+    out = gdr.preprocess_graph(x_adj)
+    assert np.array_equal(out.indptr, g["ahat_indptr"])          # degree-normalisation indices: bit-exact
+    assert np.array_equal(out.indices, g["ahat_indices"])
+    np.testing.assert_allclose(out.data, g["ahat_data"], rtol=4e-16, atol=0)   # fp64, <= 2 ulp
+    # after the fp32 cast the model sees (helper.py:95) the values are identical
+    assert np.array_equal(out.data.astype(np.float32), g["ahat_data"].astype(np.float32))
+    t = gdr.convert_sparse_matrix_to_sparse_tensor(out)
+    assert np.array_equal(t._indices().numpy(), g["coo_indices"])
+    assert np.array_equal(t._values().numpy(), g["coo_values"])
+    assert not t.is_coalesced()
+
+
+def test_preprocess_graph_with_stored_diagonal_and_isolated_rows(gdr):
+    m = random_csr(300, 300, 0.03, seed=11)
+    m = (m + sp.diags(np.where(np.arange(300) % 3 == 0, 0.5, 0.0))).tocsr()
+    m.eliminate_zeros()
+    exp = gcn_oracle.preprocess_graph(m)
+    exp.sort_indices()
+    out = gdr.preprocess_graph(m)
+    assert np.array_equal(out.indptr, exp.indptr) and np.array_equal(out.indices, exp.indices)
+    np.testing.assert_allclose(out.data, exp.data, rtol=4e-16, atol=0)
+
+
+# ---- SpMM ------------------------------------------------------------------------------------------
+@pytest.mark.parametrize("d", [4, 64, 128, 256, 512, 200])
+@pytest.mark.parametrize("n,density", [(513, 0.02), (3000, 0.004)])
+def test_spmm_f32_matches_torch_sparse_mm(gdr, n, d, density):
+    m = random_csr(n, n, density, seed=d + n)
+    # one hub row (longer than a 32-entry chunk, not a multiple of 4)
+    hub = sp.csr_matrix((np.full(n - 3, 0.25), (np.zeros(n - 3, dtype=int), np.arange(n - 3))), shape=(n, n))
+    m = (m + hub).tocsr()
+    adj_cpu = gcn_oracle.to_sparse_tensor(m)
+    x = torch.randn(n, d, generator=torch.Generator().manual_seed(d))
+    exp = torch.sparse.mm(adj_cpu, x)
+    csr = gdr.device_csr_of(adj_cpu.cuda())
+    got = csr.spmm(x.to(DEV))
+    assert_close(got.cpu().numpy(), exp.numpy(), what=f"spmm d={d}")
+    # transposed operator = autograd's Âᵀ·G
+    exp_t = torch.sparse.mm(adj_cpu.t(), x)
+    got_t = csr.transpose().spmm(x.to(DEV))
+    assert_close(got_t.cpu().numpy(), exp_t.numpy(), what=f"spmm_T d={d}")
+
+
+@pytest.mark.parametrize("d", [128, 256, 68])
+def test_spmm_fused_operands(gdr, d):
+    n = 700
+    m = random_csr(n, n, 0.01, seed=5)
+    adj_cpu = gcn_oracle.to_sparse_tensor(m)
+    g = torch.Generator().manual_seed(1)
+    x, p, e1, e2 = (torch.randn(n, d, generator=g) for _ in range(4))
+    csr = gdr.device_csr_of(adj_cpu.cuda())
+    exp_mul = torch.sparse.mm(adj_cpu, torch.mul(p, x))          # model.py:168-169
+    assert_close(csr.spmm(p.to(DEV), mul=x.to(DEV)).cpu().numpy(), exp_mul.numpy(), what="spmm mul")
+    exp_add = torch.sparse.mm(adj_cpu, x) + e1 * e2
+    assert_close(csr.spmm(x.to(DEV), e1=e1.to(DEV), e2=e2.to(DEV)).cpu().numpy(), exp_add.numpy(), what="spmm add")
+    exp_both = torch.sparse.mm(adj_cpu, p * x) + e1 * e2
+    got = csr.spmm(p.to(DEV), mul=x.to(DEV), e1=e1.to(DEV), e2=e2.to(DEV))
+    assert_close(got.cpu().numpy(), exp_both.numpy(), what="spmm mul+add")
+
+
+@pytest.mark.parametrize("d", [2, 64, 128, 256, 100])
+def test_spmm_f64_matches_scipy(gdr, d):
+    n = 900
+    m = random_csr(n, n, 0.01, seed=3)
+    x = np.random.default_rng(d).standard_normal((n, d))
+    csr = gdr.DeviceCSR.from_scipy(m, DEV, dtype=torch.float64)
+    got = csr.spmm(torch.from_numpy(x).to(DEV)).cpu().numpy()
+    np.testing.assert_allclose(got, m @ x, rtol=1e-13, atol=1e-14)
+
+
+# ---- layer / network / loss against the reference goldens ---------------------------------------------
+def _model_from_golden(gdr, g, d):
+    model = gdr.ResidualGraphConvolutionalNetwork(64, 64, num_layers=int(g["num_layers"]), hidden_units=d,
+                                                  init_weights=1e-5, layer_decay=float(g["layer_decay"]))
+    with torch.no_grad():
+        model.gcn_layer.dense.weight.copy_(torch.from_numpy(g["w_init"]))
+        model.gcn_layer.dense2.weight.copy_(torch.from_numpy(g["w_init"]))
+    return model.cuda()
+
+
+def _adj_from_golden(g, n):
+    return torch.sparse_coo_tensor(torch.from_numpy(g["coo_indices"]), torch.from_numpy(g["coo_values"]),
+                                   (n, n)).cuda()
+
+
+def test_layer_forward_matches_reference(gdr):
+    g = load_golden("gcn_knn257.npz")
+    n, d = g["embs"].shape
+    model = _model_from_golden(gdr, g, d)
+    adj = _adj_from_golden(g, n)
+    x = torch.from_numpy(g["embs"]).cuda()
+    pre, out = model.gcn_layer(x, adj)
+    assert_close(pre.detach().cpu().numpy(), g["layer1_Z"], what="pre_nonlinearity")
+    assert_close(out.detach().cpu().numpy(), g["layer1_Y"], what="output")
+    csr = gdr.device_csr_of(adj)
+    p = csr.spmm(x)
+    assert_close(p.cpu().numpy(), g["layer1_P"], what="P")
+    assert_close(csr.spmm(p, mul=x).cpu().numpy(), g["layer1_T"], what="T")
+
+
+def test_parameter_names_and_init_follow_reference(gdr):
+    g = load_golden("gcn_knn257.npz")
+    torch.manual_seed(1)
+    np.random.seed(1)
+    model = gdr.ResidualGraphConvolutionalNetwork(64, 257, num_layers=2, hidden_units=128, init_weights=1e-5,
+                                                  layer_decay=0.3)
+    assert [k for k, _ in model.named_parameters()] == [
+        "gcn_layer.dense.weight", "gcn_layer.dense.bias", "gcn_layer.dense2.weight", "gcn_layer.dense2.bias"]
+    assert np.array_equal(model.gcn_layer.dense.weight.detach().numpy(), g["w_init"])
+    assert np.array_equal(model.gcn_layer.dense2.weight.detach().numpy(), g["w_init"])
+    assert torch.count_nonzero(model.gcn_layer.dense.bias).item() == 0
+
+
+@pytest.mark.parametrize("case", ["gcn_knn257.npz", "gcn_knn600_l3.npz", "gcn_edge300_d256.npz"])
+def test_training_steps_match_reference(gdr, case):
+    """train.py:155-184 driven through the drop-in classes: forward, loss, backward, torch Adam, 3 steps."""
+    g = load_golden(case)
+    n, d = g["embs"].shape
+    model = _model_from_golden(gdr, g, d)
+    adj = _adj_from_golden(g, n)
+    x = torch.from_numpy(g["embs"]).cuda()
+    opt = torch.optim.Adam(model.parameters(), lr=float(g["lr"]), weight_decay=0)
+    loss_fcn = gdr.GSS_loss(float(g["alpha"])).gss_loss
+    beta = float(g["beta"])
+    sizes = g["batch_sizes"]
+    offs = np.concatenate([[0], np.cumsum(sizes)])
+    losses = []
+    for it in range(len(sizes)):
+        batch = torch.from_numpy(g["batches_flat"][offs[it]:offs[it + 1]]).cuda()
+        h = model(x=x, adj=adj)
+        loss = loss_fcn(embs=h, beta=beta, index=batch.detach())
+        opt.zero_grad()
+        loss.backward()
+        if it == 0:
+            if "h_step0" in g.files:
+                assert_close(h.detach().cpu().numpy(), g["h_step0"], what="hidden_emb step0")
+            for name, p in zip(("dw1", "db1", "dw2", "db2"), model.parameters()):
+                assert_close(p.grad.cpu().numpy(), g[f"{name}_step0"], what=f"{name} step0")
+        if it == len(sizes) - 1:
+            assert_close(h.detach().cpu().numpy(), g["h_last"], what="hidden_emb last")
+            for name, p in zip(("dw1", "db1", "dw2", "db2"), model.parameters()):
+                assert_close(p.grad.cpu().numpy(), g[f"{name}_last"], what=f"{name} last")
+        opt.step()
+        losses.append(loss.item())
+    assert_close(np.array(losses), g["losses"], what="losses")
+    for name, p in zip(("w1", "b1", "w2", "b2"), model.parameters()):
+        assert_close(p.detach().cpu().numpy(), g[f"{name}_final"], what=f"{name} after 3 Adam steps")
+    h_all = model(x=x, adj=adj)
+    assert_close(loss_fcn(embs=h_all, beta=beta).item(), g["loss_all"], what="loss over all rows")
+
+
+def test_input_gradient_and_oracle_autograd(gdr):
+    """Gradient w.r.t. the input features (not needed by train.py, but part of the autograd contract)."""
+    n, d = 400, 128
+    m = gcn_oracle.preprocess_graph(random_csr(n, n, 0.02, seed=2, empty_rows=False))
+    adj_cpu = gcn_oracle.to_sparse_tensor(m)
+    gen = torch.Generator().manual_seed(4)
+    x = torch.randn(n, d, generator=gen)
+    w1 = torch.eye(d) + 0.05 * torch.randn(d, d, generator=gen)
+    w2 = torch.eye(d) + 0.05 * torch.randn(d, d, generator=gen)
+    b1, b2 = 0.1 * torch.randn(d, generator=gen), 0.1 * torch.randn(d, generator=gen)
+    idx = torch.randperm(n, generator=gen)[:150]
+    xo = x.clone().requires_grad_(True)
+    ps = [t.clone().requires_grad_(True) for t in (w1, b1, w2, b2)]
+    ho = gcn_oracle.network_forward(xo, adj_cpu, *ps, num_layers=2, layer_decay=0.3)
+    lo = gcn_oracle.gss_loss(ho, 0.3, 1.0, idx)
+    lo.backward()
+    model = gdr.ResidualGraphConvolutionalNetwork(1, 1, num_layers=2, hidden_units=d, layer_decay=0.3).cuda()
+    with torch.no_grad():
+        for p, v in zip(model.parameters(), (w1, b1, w2, b2)):
+            p.copy_(v)
+    xg = x.clone().cuda().requires_grad_(True)
+    hg = model(xg, adj_cpu.cuda())
+    lg = gdr.GSS_loss(1.0).gss_loss(hg, 0.3, idx.cuda())
+    lg.backward()
+    assert_close(hg.detach().cpu().numpy(), ho.detach().numpy(), what="H")
+    assert_close(lg.item(), lo.item(), what="loss")
+    assert_close(xg.grad.cpu().numpy(), xo.grad.numpy(), what="dX")
+    for p, q, nm in zip(model.parameters(), ps, ("dW1", "db1", "dW2", "db2")):
+        assert_close(p.grad.cpu().numpy(), q.grad.numpy(), what=nm)
+
+
+def test_cpu_tensors_are_rejected(gdr):
+    model = gdr.ResidualGraphConvolutionalNetwork(1, 1, num_layers=2, hidden_units=128).cuda()
+    adj = gcn_oracle.to_sparse_tensor(sp.identity(10, format="csr"))
+    with pytest.raises(RuntimeError):
+        model(torch.randn(10, 128), adj)          # CPU adjacency / features: no silent slow path
+    with pytest.raises(RuntimeError):
+        model(torch.randn(10, 126).cuda(), adj.cuda())   # width not a multiple of 4
