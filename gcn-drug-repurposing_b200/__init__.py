@@ -15,10 +15,12 @@ csrc/libgdr.so, the C ABI in include/gdr.h).  The CUDA library is the only imple
 nothing here falls back to CPU or to another backend.
 """
 from . import _ffi  # noqa: F401
+from . import synth  # noqa: F401
 from .graph import DeviceCSR, device_csr_of  # noqa: F401
 from .model import GSS_GNNLayer, ResidualGraphConvolutionalNetwork, GSS_loss  # noqa: F401
 from .helper import (gen_graph, combine_graph, preprocess_graph,  # noqa: F401
                      convert_sparse_matrix_to_sparse_tensor)
 from .dataset import DiffusionDataSet, DiffusionDataLoader  # noqa: F401
+from .diffusion import DiffusionProfiles, RwrProblem  # noqa: F401
 
 __version__ = "0.1.0"

@@ -51,9 +51,9 @@ _SIGNATURES = {
     # PENDING "gdr_gram_percentile_f32": (c_i32, [c_ptr, c_i64, c_i64, c_f64, ctypes.POINTER(c_f32), c_ptr, c_i64, c_ptr]),
     # PENDING "gdr_gram_topk_f64": (c_i32, [c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr]),
     "gdr_adam_step_f32": (c_i32, [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_f32, c_f32, c_f32, c_f32, c_ptr, c_ptr]),
-    # PENDING "gdr_rwr_workspace_bytes": (c_i64, [c_i64, c_i64, c_i64, c_i64]),
-    # PENDING "gdr_rwr_solve_f64": (c_i32, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_i64,
-    # PENDING c_ptr, c_ptr, c_i64, c_f64, c_f64, c_i64, c_ptr, c_ptr, c_ptr, c_i64, c_ptr]),
+    "gdr_rwr_workspace_bytes": (c_i64, [c_i64, c_i64, c_i64]),
+    "gdr_rwr_solve_f64": (c_i32, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_i64,
+                                  c_f64, c_f64, c_i64, c_ptr, c_ptr, c_ptr, c_i64, c_ptr]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

@@ -105,8 +105,68 @@ __device__ __forceinline__ double inv_sqrt_cr(double x) {
   return fma(0.5 * e, y0, y0);
 }
 
-// merge the unit diagonal into every (sorted) row, sequential row sum in index order
-// exactly as scipy's csr sum(axis=1) does, d = rowsum^-1/2.
+// numpy's pairwise summation (numpy/_core/src/umath/loops_utils.h.src, PW_BLOCKSIZE 128), restated:
+// scipy's csr.sum(axis=1) is np.add.reduceat(data, indptr[:-1]) (scipy/sparse/_compressed.py, sum ->
+// _minor_reduce), which evaluates every row as data[0] + pairwise_sum(data[1:]).  Reproducing that
+// order makes the row sums (and through them D^-1/2) bit-identical to the reference's.
+__device__ double np_pairwise_block(const double *a, int n) {  // n <= 128
+  if (n < 8) {
+    double r = 0.0;
+    for (int i = 0; i < n; ++i) r = __dadd_rn(r, a[i]);
+    return r;
+  }
+  double r[8];
+#pragma unroll
+  for (int j = 0; j < 8; ++j) r[j] = a[j];
+  int i = 8;
+  for (; i < n - (n % 8); i += 8) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) r[j] = __dadd_rn(r[j], a[i + j]);
+  }
+  double res = __dadd_rn(__dadd_rn(__dadd_rn(r[0], r[1]), __dadd_rn(r[2], r[3])),
+                         __dadd_rn(__dadd_rn(r[4], r[5]), __dadd_rn(r[6], r[7])));
+  for (; i < n; ++i) res = __dadd_rn(res, a[i]);
+  return res;
+}
+
+// explicit-stack version of the recursion  f(a,n) = n<=128 ? block : f(a,n2) + f(a+n2,n-n2),
+// n2 = n/2 rounded down to a multiple of 8.  Post-order evaluation with a value stack.
+__device__ double np_pairwise_sum(const double *a, int n) {
+  if (n <= 128) return np_pairwise_block(a, n);
+  // frames: (offset, length, state) ; depth <= log2(2^31/128)+1 < 28
+  int off[28], len[28];
+  unsigned char st[28];
+  double val[28];
+  int sp = 0, vp = 0;
+  off[0] = 0, len[0] = n, st[0] = 0;
+  while (sp >= 0) {
+    const int o = off[sp], l = len[sp];
+    if (l <= 128) {
+      val[vp++] = np_pairwise_block(a + o, l);
+      --sp;
+      continue;
+    }
+    int n2 = l / 2;
+    n2 -= n2 % 8;
+    if (st[sp] == 0) {          // descend left
+      st[sp] = 1;
+      ++sp;
+      off[sp] = o, len[sp] = n2, st[sp] = 0;
+    } else if (st[sp] == 1) {   // descend right
+      st[sp] = 2;
+      ++sp;
+      off[sp] = o + n2, len[sp] = l - n2, st[sp] = 0;
+    } else {                    // combine
+      const double rgt = val[--vp], lft = val[--vp];
+      val[vp++] = __dadd_rn(lft, rgt);
+      --sp;
+    }
+  }
+  return val[0];
+}
+
+// merge the unit diagonal into every (sorted) row (scipy's A + eye), then the row sum in the
+// reference's order: row[0] + pairwise_sum(row[1:]); d = rowsum^-1/2.
 __global__ void add_identity_rowsum_kernel(const int32_t *__restrict__ rowptr, const int32_t *__restrict__ col,
                                            const double *__restrict__ val, int64_t n,
                                            const int32_t *__restrict__ out_rowptr, int32_t *__restrict__ out_col,
@@ -114,9 +174,9 @@ __global__ void add_identity_rowsum_kernel(const int32_t *__restrict__ rowptr, c
   int64_t r = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
   if (r >= n) return;
   int32_t s = rowptr[r], e = rowptr[r + 1];
-  int32_t o = out_rowptr[r];
+  const int32_t o0 = out_rowptr[r];
+  int32_t o = o0;
   bool placed = false;
-  double sum = 0.0;
   for (int32_t j = s; j < e; ++j) {
     int32_t c = col[j];
     double v = val[j];
@@ -127,20 +187,20 @@ __global__ void add_identity_rowsum_kernel(const int32_t *__restrict__ rowptr, c
       } else {
         out_col[o] = (int32_t)r;
         out_val[o] = 1.0;
-        sum += 1.0;
         ++o;
       }
     }
     out_col[o] = c;
     out_val[o] = v;
-    sum += v;
     ++o;
   }
   if (!placed) {
     out_col[o] = (int32_t)r;
     out_val[o] = 1.0;
-    sum += 1.0;
+    ++o;
   }
+  const int cnt = o - o0;  // >= 1
+  const double sum = cnt > 1 ? __dadd_rn(out_val[o0], np_pairwise_sum(out_val + o0 + 1, cnt - 1)) : out_val[o0];
   dis[r] = inv_sqrt_cr(sum);
 }
 
@@ -213,12 +273,16 @@ int gdr_csr_from_coo(const int64_t *coo_row, const int64_t *coo_col, int64_t nnz
 
 int gdr_permute_values(const void *values_in, const int64_t *perm, int64_t nnz, int elem_bytes,
                        void *values_out, gdr_stream_t stream) {
-  GDR_CHECK_ARG(nnz >= 0 && (elem_bytes == 4 || elem_bytes == 8), GDR_E_BADARG, "permute_values: bad args");
+  GDR_CHECK_ARG(nnz >= 0 && (elem_bytes == 1 || elem_bytes == 4 || elem_bytes == 8), GDR_E_BADARG,
+                "permute_values: bad args");
   if (nnz == 0) return GDR_OK;
   GDR_CHECK_ARG(values_in && perm && values_out, GDR_E_BADARG, "permute_values: null pointer");
   const int T = 256;
   unsigned g = (unsigned)ceil_div<int64_t>(nnz, T);
-  if (elem_bytes == 4)
+  if (elem_bytes == 1)
+    permute_kernel<uint8_t><<<g, T, 0, as_stream(stream)>>>((const uint8_t *)values_in, perm, nnz,
+                                                           (uint8_t *)values_out);
+  else if (elem_bytes == 4)
     permute_kernel<uint32_t><<<g, T, 0, as_stream(stream)>>>((const uint32_t *)values_in, perm, nnz,
                                                             (uint32_t *)values_out);
   else

@@ -89,22 +89,27 @@ class DeviceCSR:
     # ---- transpose ----------------------------------------------------------------------------
     def transpose(self):
         if self._t is None:
-            L = _ffi.lib()
-            dev = self.device
-            nnz = self.nnz
-            t_rowptr = torch.empty(self.n_cols + 1, dtype=torch.int32, device=dev)
-            t_col = torch.empty(max(nnz, 1), dtype=torch.int32, device=dev)[:nnz]
-            perm = torch.empty(max(nnz, 1), dtype=torch.int64, device=dev)[:nnz]
-            ws = _ffi.workspace(L.gdr_csr_transpose_workspace_bytes(nnz, self.n_rows, self.n_cols), dev)
-            _ffi.check(L.gdr_csr_transpose(_ffi.ptr(self.rowptr), _ffi.ptr(self.col), nnz, self.n_rows, self.n_cols,
-                                           _ffi.ptr(t_rowptr), _ffi.ptr(t_col), _ffi.ptr(perm), _ffi.ptr(ws),
-                                           ws.numel(), _ffi.stream()), "csr_transpose")
-            t_val = torch.empty_like(self.val)
-            _ffi.check(L.gdr_permute_values(_ffi.ptr(self.val), _ffi.ptr(perm), nnz, self.val.element_size(),
-                                            _ffi.ptr(t_val), _ffi.stream()), "permute_values")
-            self._t = DeviceCSR(t_rowptr, t_col, t_val, self.n_cols, self.n_rows)
-            self._t._t = self
+            self.transpose_with_perm()
         return self._t
+
+    def transpose_with_perm(self):
+        """(transposed DeviceCSR, perm int64[nnz]) with perm[i] = position in self of transposed entry i."""
+        L = _ffi.lib()
+        dev = self.device
+        nnz = self.nnz
+        t_rowptr = torch.empty(self.n_cols + 1, dtype=torch.int32, device=dev)
+        t_col = torch.empty(max(nnz, 1), dtype=torch.int32, device=dev)[:nnz]
+        perm = torch.empty(max(nnz, 1), dtype=torch.int64, device=dev)[:nnz]
+        ws = _ffi.workspace(L.gdr_csr_transpose_workspace_bytes(nnz, self.n_rows, self.n_cols), dev)
+        _ffi.check(L.gdr_csr_transpose(_ffi.ptr(self.rowptr), _ffi.ptr(self.col), nnz, self.n_rows, self.n_cols,
+                                       _ffi.ptr(t_rowptr), _ffi.ptr(t_col), _ffi.ptr(perm), _ffi.ptr(ws),
+                                       ws.numel(), _ffi.stream()), "csr_transpose")
+        t_val = torch.empty_like(self.val)
+        _ffi.check(L.gdr_permute_values(_ffi.ptr(self.val), _ffi.ptr(perm), nnz, self.val.element_size(),
+                                        _ffi.ptr(t_val), _ffi.stream()), "permute_values")
+        self._t = DeviceCSR(t_rowptr, t_col, t_val, self.n_cols, self.n_rows)
+        self._t._t = self
+        return self._t, perm
 
     # ---- (A + I) symmetric normalisation: preprocess_graph on the device -----------------------
     def normalized_with_identity(self):

@@ -55,7 +55,7 @@ int gdr_csr_from_coo(const int64_t *coo_row, const int64_t *coo_col, int64_t nnz
                      int64_t n_rows, int64_t n_cols, int32_t *rowptr_out,
                      int32_t *col_out, int64_t *perm_out, void *workspace,
                      int64_t workspace_bytes, gdr_stream_t stream);
-/* values_out[i] = values_in[perm[i]] (elem_bytes 4 or 8) */
+/* values_out[i] = values_in[perm[i]] (elem_bytes 1, 4 or 8) */
 int gdr_permute_values(const void *values_in, const int64_t *perm, int64_t nnz,
                        int elem_bytes, void *values_out, gdr_stream_t stream);
 
@@ -168,28 +168,28 @@ int gdr_adam_step_f32(float *param, const float *grad, float *exp_avg, float *ex
                       int32_t *step_dev, gdr_stream_t stream);
 
 /* ---- diffusion profiles (multiscale/diff_prof/diffusion_profiles.py:29-90) ----------- *
- * Batched personalised-PageRank power iteration for `n_seeds` seeds, each with the
- * reference's per-seed matrix surgery (all other drugs/indications become sinks; edges
- * protein->seed removed; rows renormalised).  See gdr_rwr.h-style comment in rwr.cu.
- *   M   : CSR of the weighted MSI adjacency (rows = sources), fp64.
- *   Mt  : CSR of its transpose (rows = targets), values permuted accordingly.
- *   is_sink[n]       : 1 for every drug/indication node.
- *   seed_node[s]     : node index of seed s.
- *   rm_ptr[s..s+1], rm_node[] : for seed s the source nodes u whose edge u->seed is
- *                      deleted (the reference's drug_or_indication2proteins[seed]).
- *   x_out [n_seeds, n]: diffusion profiles (row s = profile of seed s).
- *   iters_out[n_seeds]: iteration at which each seed met ||dx||_1 < n*tol.
- * Synchronises the stream.  Returns GDR_E_NOCONV if any seed hit max_iter.             */
-int64_t gdr_rwr_workspace_bytes(int64_t n, int64_t nnz, int64_t n_seeds,
-                                int64_t n_removed);
+ * Batched personalised-PageRank power iteration for `n_seeds` seeds at once, each with the
+ * reference's per-seed matrix surgery applied on the fly (never materialised):
+ *   convert_M_to_make_all_drugs_indications_sinks_except_selected (:29-47), refine_M_S (:49-56),
+ *   power_iteration (:65-90).
+ *   M   : CSR of the weighted MSI adjacency, M[u,v] = w(u->v) (get_initial_M, :21-27), fp64,
+ *         sorted rows.  Mt: CSR of its transpose (gdr_csr_transpose: sources ascending).
+ *   *_flag[e] (uint8 per stored entry, same order as the matching val array):
+ *         bit0: entry (t,p), t a drug/indication and p in drug_or_indication2proteins[t]
+ *               -> zero for every seed except t itself                        (:39-46)
+ *         bit1: entry (p,t), same pairs -> zero for seed t only               (:33-36)
+ *   seed_node[s]     : node index of seed s (personalisation = one-hot, :58-63).
+ *   x_out [n_seeds, n]: diffusion profiles (row s = what the reference np.save()s for seed s).
+ *   iters_out[n_seeds]: iteration (1-based) at which each seed met ||dx||_1 < n*tol.
+ * Synchronises the stream once per iteration (convergence count).  Returns GDR_E_NOCONV if any
+ * seed hit max_iter (the reference raises, :90).                                           */
+int64_t gdr_rwr_workspace_bytes(int64_t n, int64_t nnz, int64_t n_seeds);
 int gdr_rwr_solve_f64(const int32_t *m_rowptr, const int32_t *m_col, const double *m_val,
-                      const int32_t *mt_rowptr, const int32_t *mt_col,
-                      const double *mt_val, int64_t n, int64_t nnz,
-                      const uint8_t *is_sink, const int32_t *seed_node, int64_t n_seeds,
-                      const int32_t *rm_ptr, const int32_t *rm_node, int64_t n_removed,
-                      double alpha, double tol, int64_t max_iter, double *x_out,
-                      int32_t *iters_out, void *workspace, int64_t workspace_bytes,
-                      gdr_stream_t stream);
+                      const uint8_t *m_flag, const int32_t *mt_rowptr, const int32_t *mt_col,
+                      const double *mt_val, const uint8_t *mt_flag, int64_t n, int64_t nnz,
+                      const int32_t *seed_node, int64_t n_seeds, double alpha, double tol,
+                      int64_t max_iter, double *x_out, int32_t *iters_out, void *workspace,
+                      int64_t workspace_bytes, gdr_stream_t stream);
 
 #ifdef __cplusplus
 }
