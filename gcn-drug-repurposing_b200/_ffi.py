@@ -47,9 +47,9 @@ _SIGNATURES = {
     "gdr_gss_loss_fwd_bwd_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_f32, c_f32, c_ptr, c_ptr, c_ptr,
                                          c_i64, c_ptr]),
     "gdr_scatter_rows_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr]),
-    # PENDING "gdr_gram_percentile_workspace_bytes": (c_i64, [c_i64, c_i64]),
-    # PENDING "gdr_gram_percentile_f32": (c_i32, [c_ptr, c_i64, c_i64, c_f64, ctypes.POINTER(c_f32), c_ptr, c_i64, c_ptr]),
-    # PENDING "gdr_gram_topk_f64": (c_i32, [c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr]),
+    "gdr_gram_percentile_workspace_bytes": (c_i64, [c_i64, c_i64]),
+    "gdr_gram_percentile_f32": (c_i32, [c_ptr, c_i64, c_i64, c_f64, ctypes.POINTER(c_f32), c_ptr, c_i64, c_ptr]),
+    "gdr_gram_topk_f64": (c_i32, [c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr]),
     "gdr_adam_step_f32": (c_i32, [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_f32, c_f32, c_f32, c_f32, c_ptr, c_ptr]),
     "gdr_rwr_workspace_bytes": (c_i64, [c_i64, c_i64, c_i64]),
     "gdr_rwr_solve_f64": (c_i32, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_i64,

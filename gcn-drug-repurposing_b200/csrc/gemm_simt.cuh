@@ -4,13 +4,42 @@
 // contractions; the tcgen05 3xTF32 variant lives in gemm_tc.cu and replaces this kernel
 // where it has been validated.
 #pragma once
+#include <string.h>
+
 #include "common.cuh"
 
 namespace gdr {
 
 constexpr int GBM = 128, GBN = 128, GBK = 16, GTHREADS = 256, GPAD = 4;
 
-enum GemmEpi { EPI_STORE = 0, EPI_LAYER = 1, EPI_SPLITK = 2, EPI_GSS = 3 };
+enum GemmEpi { EPI_STORE = 0, EPI_LAYER = 1, EPI_SPLITK = 2, EPI_GSS = 3, EPI_HIST = 4, EPI_MINGT = 5 };
+
+constexpr int GHIST_BINS = 2048;
+
+// radix-select state of the Gram order-statistic search (gram.cu)
+struct SelectState {
+  unsigned int prefix;       // key bits fixed so far
+  unsigned int mask;         // which bits those are
+  unsigned long long rank;   // rank still to descend inside the prefix bucket
+  unsigned long long count;  // population of the bucket chosen last
+  unsigned int min_gt;       // EPI_MINGT: smallest key strictly above `prefix`
+};
+
+// order-preserving fp32 -> uint32 key
+__device__ __forceinline__ unsigned int f32_key(float v) {
+  const unsigned int b = __float_as_uint(v);
+  return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__host__ __device__ __forceinline__ float f32_from_key(unsigned int k) {
+  const unsigned int b = (k & 0x80000000u) ? (k & 0x7fffffffu) : ~k;
+#ifdef __CUDA_ARCH__
+  return __uint_as_float(b);
+#else
+  float f;
+  memcpy(&f, &b, 4);
+  return f;
+#endif
+}
 
 struct GemmParams {
   // up to two K-segments: C = sum_s A_s · B_sᵀ   (A_s(m,k), B_s(n,k))
@@ -32,6 +61,13 @@ struct GemmParams {
   // EPI_GSS
   float alpha, beta, wscale;
   double *loss_partials;  // one per CTA
+  // EPI_HIST / EPI_MINGT (symmetric Gram: only tiles with blockIdx.x >= blockIdx.y run, off-diagonal
+  // tiles count twice)
+  const SelectState *sel;
+  unsigned long long *hist;  // [GHIST_BINS]
+  int shift;                 // digit position of this pass
+  unsigned int bin_mask;     // (bins of this pass) - 1
+  SelectState *sel_out;      // EPI_MINGT: atomicMin target
 };
 
 __device__ __forceinline__ float elu1(float z) { return z > 0.f ? z : expm1f(z); }
@@ -91,6 +127,9 @@ __global__ void __launch_bounds__(GTHREADS) gemm_f32_kernel(const GemmParams p) 
   __shared__ __align__(16) float As[2][GBK][GBM + GPAD];
   __shared__ __align__(16) float Bs[2][GBK][GBN + GPAD];
 
+  if (EPI == EPI_HIST || EPI == EPI_MINGT) {
+    if (blockIdx.x < blockIdx.y) return;  // symmetric: the mirrored tile is counted by weight 2
+  }
   const int t = threadIdx.x;
   const int tx = t & 15, ty = t >> 4;
   const int64_t m0 = (int64_t)blockIdx.y * GBM;
@@ -151,6 +190,51 @@ __global__ void __launch_bounds__(GTHREADS) gemm_f32_kernel(const GemmParams p) 
   }
 
   // ---- epilogue ----------------------------------------------------------------------
+  if (EPI == EPI_HIST) {
+    __shared__ unsigned int sh_hist[GHIST_BINS];
+    for (int i = t; i < GHIST_BINS; i += GTHREADS) sh_hist[i] = 0u;
+    __syncthreads();
+    const unsigned int prefix = p.sel->prefix, mask = p.sel->mask;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int64_t m = m0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
+      if (m >= p.m) continue;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int64_t n = n0 + (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
+        if (n >= p.n) continue;
+        const unsigned int key = f32_key(acc[i][j]);
+        if ((key & mask) == prefix) atomicAdd(&sh_hist[(key >> p.shift) & p.bin_mask], 1u);
+      }
+    }
+    __syncthreads();
+    const unsigned long long w = (blockIdx.x == blockIdx.y) ? 1ull : 2ull;
+    for (int i = t; i < GHIST_BINS; i += GTHREADS) {
+      const unsigned int c = sh_hist[i];
+      if (c) atomicAdd(p.hist + i, w * c);
+    }
+    return;
+  }
+  if (EPI == EPI_MINGT) {
+    const unsigned int base = p.sel->prefix;
+    unsigned int best = 0xffffffffu;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) {
+      const int64_t m = m0 + (i < 4 ? ty * 4 + i : 64 + ty * 4 + (i - 4));
+      if (m >= p.m) continue;
+#pragma unroll
+      for (int j = 0; j < 8; ++j) {
+        const int64_t n = n0 + (j < 4 ? tx * 4 + j : 64 + tx * 4 + (j - 4));
+        if (n >= p.n) continue;
+        const unsigned int key = f32_key(acc[i][j]);
+        if (key > base) best = min(best, key);
+      }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+    if ((t & 31) == 0 && best != 0xffffffffu) atomicMin(&p.sel_out->min_gt, best);
+    return;
+  }
   double lsum = 0.0;
 #pragma unroll
   for (int i = 0; i < 8; ++i) {

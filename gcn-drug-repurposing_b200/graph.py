@@ -16,6 +16,10 @@ from . import _ffi
 
 
 class DeviceCSR:
+    # benchmark hook: when set to a list, every spmm() appends
+    # (start_event, end_event, nnz, n_rows, d, has_mul, has_add) recorded on the launching stream
+    timer = None
+
     def __init__(self, rowptr, col, val, n_rows, n_cols):
         self.rowptr = rowptr  # int32 [n_rows+1]
         self.col = col        # int32 [nnz]
@@ -154,6 +158,10 @@ class DeviceCSR:
         d = x.shape[1]
         if out is None:
             out = torch.empty(self.n_rows, d, dtype=x.dtype, device=x.device)
+        rec = DeviceCSR.timer
+        if rec is not None:
+            ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            ev0.record()
         if x.dtype == torch.float32:
             _ffi.check(L.gdr_spmm_csr_f32(_ffi.ptr(self.rowptr), _ffi.ptr(self.col), _ffi.ptr(self.val), self.n_rows,
                                           d, _ffi.ptr(x), _ffi.ptr(mul), _ffi.ptr(e1), _ffi.ptr(e2), _ffi.ptr(out),
@@ -165,6 +173,9 @@ class DeviceCSR:
                                           d, _ffi.ptr(x), _ffi.ptr(out), _ffi.stream()), "spmm_csr_f64")
         else:
             raise RuntimeError(f"spmm: unsupported dtype {x.dtype}")
+        if rec is not None:
+            ev1.record()
+            rec.append((ev0, ev1, self.nnz, self.n_rows, d, mul is not None, e1 is not None))
         return out
 
 

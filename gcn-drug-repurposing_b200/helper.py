@@ -38,6 +38,22 @@ def gram_topk(x_rows, k):
     return idx, val
 
 
+def gram_percentile(h, q):
+    """np.percentile(np.dot(h, h.T).flatten(), q) of train.py:165-167 for an fp32 CUDA tensor h [n, d],
+    by radix select over recomputed Gram tiles (N×N is never stored).  Returns numpy.float32 like numpy."""
+    import ctypes
+    L = _ffi.lib()
+    if not h.is_cuda or h.dtype != torch.float32:
+        raise RuntimeError("gram_percentile: expected an fp32 CUDA tensor (no CPU implementation)")
+    h = h.contiguous()
+    n, d = h.shape
+    ws = _ffi.workspace(L.gdr_gram_percentile_workspace_bytes(n, d), h.device)
+    out = ctypes.c_float(0.0)
+    _ffi.check(L.gdr_gram_percentile_f32(_ffi.ptr(h), n, d, float(q), ctypes.byref(out), _ffi.ptr(ws), ws.numel(),
+                                         _ffi.stream()), "gram_percentile_f32")
+    return np.float32(out.value)
+
+
 def knn_adjacency(x_rows, k):
     """Symmetrised kNN adjacency of helpers/helper.py:39-53 as a scipy CSR (fp64, empty diagonal):
     x_adj[i, j] = x_adj[j, i] = <x_i, x_j> for j in top-k(i); the diagonal is cleared."""

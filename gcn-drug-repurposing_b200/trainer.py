@@ -1,0 +1,145 @@
+"""train.py of the reference (train.py:72-193) restated on the drop-in classes.
+
+    main(args)        the reference driver, line for line, minus what cannot run on current numpy
+                      (np.float, :80) — same flags (parse_args mirrors train.py:12-59), same order of
+                      RNG draws, same `graph_embs.txt` output (np.savetxt, '%.18e', headerless).
+    GCNTrainer        the loop body (train.py:151-187) as an object, for benchmarks and tests: one
+                      `iteration(batch)` = full-graph forward + batch GSS loss + backward + Adam.
+
+Everything numeric goes through gcn-drug-repurposing_b200's classes, i.e. libgdr.so; there is no CPU path.
+"""
+import argparse
+import time
+
+import numpy as np
+import torch
+
+from .dataset import DiffusionDataLoader, DiffusionDataSet
+from .helper import (combine_graph, convert_sparse_matrix_to_sparse_tensor, gen_graph, gram_percentile,
+                     preprocess_graph)
+from .model import GSS_loss, ResidualGraphConvolutionalNetwork
+
+
+def build_parser():
+    """train.py:12-58, flag for flag (defaults included)."""
+    p = argparse.ArgumentParser(description='GCN similarity-loss embedding on a B200')
+    p.add_argument('--emb-file', type=str, required=True, help='node2vec-format .embs.txt (train.py:79)')
+    p.add_argument('--epochs', type=int, default=20)
+    p.add_argument('--lr', type=float, default=0.0001)
+    p.add_argument('--batch-size', type=int, default=0)
+    p.add_argument('--num-layers', type=int, default=2)
+    p.add_argument('--hidden-units', type=int, default=2048)
+    p.add_argument('--init-weights', type=float, default=1e-5)
+    p.add_argument('--layer-decay', type=float, default=0.3)
+    p.add_argument('--regularizer-scale', type=float, default=0.0)
+    p.add_argument('--k', type=int, default=5)
+    p.add_argument('--kq', type=int, default=5)
+    p.add_argument('--alpha', type=float, default=1.0)
+    p.add_argument('--beta', type=float, default=None)
+    p.add_argument('--beta-percentile', type=float, default=None)
+    p.add_argument('--graph-mode', type=str, default='descriptor')
+    p.add_argument('--loss', type=str, default='gss')
+    p.add_argument('--seed', type=int, default=0)
+    p.add_argument('--gpu-id', type=int, default=0)
+    p.add_argument('--out-file', type=str, default='graph_embs.txt', help="train.py:193 hard-codes this name")
+    return p
+
+
+def load_embs(path):
+    """train.py:79-82: skip the 'N dim' header, drop the node-name column, fp64."""
+    with open(path) as f:
+        next(f)
+        rows = [np.array(line.split()[1:], dtype=np.float64) for line in f if line.strip()]
+    return np.stack(rows)
+
+
+class GCNTrainer:
+    """Model + optimizer + loss of train.py:111-150, features and adjacency resident on the device."""
+
+    def __init__(self, features, adj, hidden_units, num_layers=2, layer_decay=0.3, init_weights=1e-5, alpha=1.0,
+                 lr=3e-4, batch_size=2048, beta=None, beta_percentile=None, device="cuda"):
+        self.device = torch.device(device)
+        self.dataset = DiffusionDataSet(features=features, adj=adj.to(self.device))
+        n = len(self.dataset)
+        self.batch_size = batch_size if batch_size > 0 else n
+        self.model = ResidualGraphConvolutionalNetwork(train_batch_size=self.batch_size, val_batch_size=n,
+                                                       num_layers=num_layers, hidden_units=hidden_units,
+                                                       init_weights=init_weights, layer_decay=layer_decay)
+        self.model.to(self.device)
+        self.model.train()
+        self.optimizer = torch.optim.Adam(self.model.parameters(), lr=lr, weight_decay=0)
+        self.loss_fcn = GSS_loss(alpha).gss_loss
+        self.beta = beta
+        self.beta_percentile = beta_percentile
+        self.features_dev = self.dataset.features.to(self.device)
+        self.hidden_emb = None
+
+    def loader(self, shuffle=True):
+        return DiffusionDataLoader(self.dataset, batch_size=self.batch_size, num_workers=6, shuffle=shuffle)
+
+    def select_beta(self, hidden_emb):
+        """train.py:163-172."""
+        if self.beta_percentile is not None:
+            return gram_percentile(hidden_emb.detach(), self.beta_percentile)
+        if self.beta is not None:
+            return self.beta
+        raise Exception('At least one of beta and beta_percentile should be set!')
+
+    def iteration(self, batch, features=None):
+        """train.py:157-184.  batch: int64 index tensor on the device."""
+        x = self.features_dev if features is None else features
+        hidden_emb = self.model(x=x, adj=self.dataset.adj)
+        if self.beta is None:
+            self.beta = self.select_beta(hidden_emb)
+        loss = self.loss_fcn(embs=hidden_emb, beta=self.beta, index=batch.detach())
+        self.optimizer.zero_grad()
+        loss.backward()
+        self.optimizer.step()
+        self.hidden_emb = hidden_emb
+        return loss
+
+    def epoch(self, batches):
+        loss = None
+        for b in batches:
+            loss = self.iteration(b)
+        return loss
+
+
+def main(args):
+    """train.py:72-193."""
+    if args.seed:
+        torch.manual_seed(args.seed)
+        np.random.seed(args.seed)
+    if args.beta is not None and args.beta_percentile is not None:
+        raise Exception('beta and beta_percentile can not be used at the same time!')
+    if args.graph_mode != 'descriptor':
+        raise Exception('ransac graph modes need the retrieval datasets, absent from the reference repository too')
+    ppi_embs = load_embs(args.emb_file)
+    X = ppi_embs.T                                   # (d, num_nodes)
+    Q = X[:, 0:3]
+    q_adj, q_features, x_adj, x_features = gen_graph(Q, X, args.kq, args.k, None, None)
+    x_adj_normed = preprocess_graph(x_adj)
+    x_adj_normed_sparse_tensor = convert_sparse_matrix_to_sparse_tensor(x_adj_normed)
+    # train.py:96-104 also builds the (N+3)-node query graph; nothing consumes it afterwards
+    _ = combine_graph(q_adj, x_adj)
+    trainer = GCNTrainer(x_features, x_adj_normed_sparse_tensor, args.hidden_units, num_layers=args.num_layers,
+                         layer_decay=args.layer_decay, init_weights=args.init_weights, alpha=args.alpha, lr=args.lr,
+                         batch_size=args.batch_size, beta=args.beta, beta_percentile=args.beta_percentile,
+                         device=f"cuda:{args.gpu_id}")
+    if args.loss != 'gss':
+        raise Exception("only the 'gss' loss is functional upstream (tri_loss references undefined names)")
+    loader = trainer.loader(shuffle=True)
+    itr = 0
+    while itr < args.epochs:
+        start_time = time.time()
+        for batch_id, batch_data in enumerate(loader):
+            trainer.iteration(batch_data.to(trainer.device))
+        train_time = time.time() - start_time  # noqa: F841  (computed and unused upstream as well)
+        itr += 1
+        print(f"iter {itr}")
+    np.savetxt(args.out_file, trainer.hidden_emb.cpu().data)
+    return trainer
+
+
+if __name__ == '__main__':
+    main(build_parser().parse_args())

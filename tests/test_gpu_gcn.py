@@ -264,3 +264,83 @@ def test_cpu_tensors_are_rejected(gdr):
         model(torch.randn(10, 128), adj)          # CPU adjacency / features: no silent slow path
     with pytest.raises(RuntimeError):
         model(torch.randn(10, 126).cuda(), adj.cuda())   # width not a multiple of 4
+
+
+# ---- Gram reductions: kNN graph (gen_graph) and the beta percentile -----------------------------------
+@pytest.mark.parametrize("case", ["gcn_knn257.npz", "gcn_knn600_l3.npz"])
+def test_gen_graph_matches_reference(gdr, case):
+    g = load_golden(case)
+    n, d = g["embs"].shape
+    k = int(g["k"])
+    X = g["embs"].astype(np.float64).T
+    q_adj, qf, x_adj, xf = gdr.gen_graph(X[:, 0:3], X, 5, k)
+    assert xf.shape == (n, d) and qf.shape == (3, d)
+    # kNN index sets: bit-exact (rows whose k-th / (k+1)-th similarities tie to fp64 rounding excepted)
+    idx, val = gdr.helper.gram_topk(torch.from_numpy(np.ascontiguousarray(X.T)).cuda(), k)
+    got = np.sort(idx.cpu().numpy(), axis=1)
+    clear = g["topk_gap"] > 1e-12
+    assert clear.mean() > 0.99
+    assert np.array_equal(got[clear], g["topk_sorted"][clear])
+    assert np.all(np.diff(val.cpu().numpy(), axis=1) <= 0)           # descending
+    # the symmetrised adjacency: structure bit-exact, values to fp64 rounding of the dot products
+    x_adj.sort_indices()
+    assert np.array_equal(x_adj.indptr, g["x_adj_indptr"])
+    assert np.array_equal(x_adj.indices, g["x_adj_indices"])
+    np.testing.assert_allclose(x_adj.data, g["x_adj_data"], rtol=1e-12)
+    q_adj.sort_indices()
+    assert np.array_equal(q_adj.indptr, g["q_adj_indptr"]) and np.array_equal(q_adj.indices, g["q_adj_indices"])
+    np.testing.assert_allclose(q_adj.data, g["q_adj_data"], rtol=1e-12)
+
+
+@pytest.mark.parametrize("n,d,k", [(64, 8, 5), (65, 20, 1), (1000, 128, 5), (777, 256, 32)])
+def test_gram_topk_vs_numpy(gdr, n, d, k):
+    x = np.random.default_rng(n).standard_normal((n, d))
+    idx, val = gdr.helper.gram_topk(torch.from_numpy(x).cuda(), k)
+    s = x @ x.T
+    exp_val = -np.sort(-s, axis=1)[:, :k]
+    np.testing.assert_allclose(val.cpu().numpy(), exp_val, rtol=1e-12, atol=1e-12)
+    got = idx.cpu().numpy()
+    np.testing.assert_allclose(np.take_along_axis(s, got.astype(np.int64), 1), exp_val, rtol=1e-12, atol=1e-12)
+    assert all(len(set(r)) == k for r in got.tolist())
+
+
+@pytest.mark.parametrize("n,d,q", [(257, 128, 98.0), (600, 128, 98.0), (300, 256, 50.0), (130, 12, 0.0), (130, 12, 100.0),
+                                   (513, 64, 99.999)])
+def test_gram_percentile_vs_numpy(gdr, n, d, q):
+    h = torch.nn.functional.normalize(torch.randn(n, d, generator=torch.Generator().manual_seed(n)), dim=1)
+    exp = np.percentile(np.dot(h.numpy(), h.numpy().T).flatten(), q)
+    got = gdr.helper.gram_percentile(h.cuda(), q)
+    assert isinstance(got, np.float32)
+    assert_close(got, exp, what=f"beta q={q}")
+
+
+@pytest.mark.parametrize("case", ["gcn_knn257.npz", "gcn_knn600_l3.npz", "gcn_edge300_d256.npz"])
+def test_beta_selection_matches_reference(gdr, case):
+    g = load_golden(case)
+    n, d = g["embs"].shape
+    model = _model_from_golden(gdr, g, d)
+    h0 = model(x=torch.from_numpy(g["embs"]).cuda(), adj=_adj_from_golden(g, n))
+    beta = gdr.helper.gram_percentile(h0.detach(), float(g["beta_percentile"]))
+    assert_close(beta, g["beta"], what="beta (train.py:166-167)")
+
+
+def test_trainer_main_writes_embs_like_train_py(gdr, tmp_path):
+    """trainer.main = train.py:72-193 on the drop-in classes; output format '%.18e', headerless, row i = node i."""
+    g = load_golden("gcn_knn257.npz")
+    emb_file = tmp_path / "in.embs.txt"
+    gdr.synth.write_node2vec_embs(str(emb_file), [f"n{i}" for i in range(len(g["embs"]))], g["embs"])
+    from gdr_b200 import trainer
+    out = tmp_path / "graph_embs.txt"
+    args = trainer.build_parser().parse_args([
+        "--emb-file", str(emb_file), "--num-layers", "2", "--hidden-units", "128", "--k", "5", "--kq", "5",
+        "--epochs", "2", "--lr", "0.0003", "--beta-percentile", "98", "--batch-size", "64", "--seed", "1",
+        "--out-file", str(out)])
+    tr = trainer.main(args)
+    assert_close(tr.beta, g["beta"], what="beta")
+    assert np.array_equal(tr.model.gcn_layer.dense.weight.detach().cpu().numpy().shape, (128, 128))
+    text = open(out).read().splitlines()
+    assert len(text) == 257 and len(text[0].split(" ")) == 128
+    assert all(len(tok) == 24 or len(tok) == 25 for tok in text[0].split(" "))      # %.18e
+    emb = np.loadtxt(str(out))
+    assert_close(emb, tr.hidden_emb.detach().cpu().numpy(), rtol=0, atol=0, what="savetxt round trip")
+    assert_close(np.linalg.norm(emb, axis=1), np.ones(257), what="unit rows")
