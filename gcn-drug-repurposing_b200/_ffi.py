@@ -34,6 +34,8 @@ _SIGNATURES = {
     "gdr_csr_add_identity_workspace_bytes": (c_i64, [c_i64]),
     "gdr_csr_normalize_f64": (c_i32, [c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
     "gdr_spmm_csr_f32": (c_i32, [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
+    "gdr_spmm_csr_planned_f32": (c_i32, [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i32,
+                                         c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr]),
     "gdr_spmm_csr_f64": (c_i32, [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr]),
     "gdr_gcn_layer_fwd_f32": (c_i32, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_f32, c_i64, c_i64,
                                       c_ptr, c_ptr, c_ptr]),

@@ -9,6 +9,8 @@
 //           torch.sparse.mm(adj, torch.mul(Ax, x))   modules/model.py:168-169 (mul folded in)
 //           autograd of both (Âᵀ·G on the transposed CSR)
 //           x * M                                     multiscale/diff_prof/diffusion_profiles.py:85
+#include <limits.h>
+
 #include "common.cuh"
 
 namespace gdr {
@@ -56,27 +58,17 @@ __device__ __forceinline__ typename VecOf<T>::type vload(const T *p) {
   return __ldg(reinterpret_cast<const typename VecOf<T>::type *>(p));
 }
 
-// One warp per row.  Row width d == 32 * VecOf<T>::N * V exactly (V slabs per lane).
-template <typename T, int V, bool MUL, bool ADD>
-__global__ void __launch_bounds__(256)
-spmm_warp_row_kernel(const int32_t *__restrict__ rowptr, const int32_t *__restrict__ col,
-                     const T *__restrict__ val, int64_t n_rows, const T *__restrict__ x,
-                     const T *__restrict__ mul, const T *__restrict__ e1, const T *__restrict__ e2,
-                     T *__restrict__ y) {
+// acc += sum_{e in [s,e)} val[e] * x[col[e], :] (* mul[col[e], :]).  The warp fetches 32 (col,val) pairs
+// at a time, broadcasts them with shuffles and keeps 4 gathered rows (4*V 128-bit loads per lane) in flight.
+template <typename T, int V, bool MUL>
+__device__ __forceinline__ void gather_range(const int32_t *__restrict__ col, const T *__restrict__ val,
+                                             const T *__restrict__ x, const T *__restrict__ mul, int32_t s,
+                                             int32_t e, int lane, typename VecOf<T>::type (&acc)[V]) {
   using Vec = typename VecOf<T>::type;
-  constexpr int EPL = VecOf<T>::N;      // elements per 16-byte lane load
-  constexpr int SLAB = 32 * EPL;        // elements per warp-wide load
+  constexpr int EPL = VecOf<T>::N;
+  constexpr int SLAB = 32 * EPL;
   constexpr int64_t D = (int64_t)SLAB * V;
-  const int lane = threadIdx.x & 31;
-  const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (row >= n_rows) return;
-  const int32_t s = rowptr[row], e = rowptr[row + 1];
   const int loff = lane * EPL;
-
-  Vec acc[V];
-#pragma unroll
-  for (int v = 0; v < V; ++v) vzero(acc[v]);
-
   for (int32_t base = s; base < e; base += 32) {
     const int32_t idx = base + lane;
     int32_t c = 0;
@@ -127,6 +119,74 @@ spmm_warp_row_kernel(const int32_t *__restrict__ rowptr, const int32_t *__restri
         vfma(acc[v], w1, t);
       }
     }
+  }
+}
+
+// Degree-aware schedule ("plan", built once per CSR by the host mirror, graph.py):
+//   rows with more than hub_threshold entries (hubs) are cut into chunks of <= chunk entries;
+//   chunk_info[c] = (hub index, first entry, end entry, 0), hub_info[h] = (row, first chunk, #chunks, 0).
+// Warps [0, n_chunks) each reduce one hub chunk into partial[c][:]; the last warp to finish a hub (an
+// atomic ticket per hub, self-resetting) adds the partials IN CHUNK ORDER, so the result does not depend on
+// scheduling.  Warps [n_chunks, n_chunks + n_rows) own one non-hub row each.  Hub chunks come first in the
+// grid so the long rows start at once instead of forming the tail of the launch.
+struct SpmmPlan {
+  int32_t hub_threshold;  // INT32_MAX: no hubs
+  int32_t n_chunks;
+  const int4 *chunk_info;
+  const int4 *hub_info;
+  int32_t *tickets;  // [n_hubs], zero on entry and on exit
+  void *partial;     // [n_chunks, d]
+};
+
+// Row width d == 32 * VecOf<T>::N * V exactly (V slabs per lane).
+template <typename T, int V, bool MUL, bool ADD>
+__global__ void __launch_bounds__(256)
+spmm_warp_row_kernel(const int32_t *__restrict__ rowptr, const int32_t *__restrict__ col,
+                     const T *__restrict__ val, int64_t n_rows, const T *__restrict__ x,
+                     const T *__restrict__ mul, const T *__restrict__ e1, const T *__restrict__ e2,
+                     T *__restrict__ y, const SpmmPlan plan) {
+  using Vec = typename VecOf<T>::type;
+  constexpr int EPL = VecOf<T>::N;      // elements per 16-byte lane load
+  constexpr int SLAB = 32 * EPL;        // elements per warp-wide load
+  constexpr int64_t D = (int64_t)SLAB * V;
+  const int lane = threadIdx.x & 31;
+  const int loff = lane * EPL;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+
+  Vec acc[V];
+#pragma unroll
+  for (int v = 0; v < V; ++v) vzero(acc[v]);
+
+  int64_t row;
+  if (warp < plan.n_chunks) {
+    // ---- one chunk of a hub row -------------------------------------------------------------------
+    const int4 ci = __ldg(plan.chunk_info + warp);
+    gather_range<T, V, MUL>(col, val, x, mul, ci.y, ci.z, lane, acc);
+    T *pp = static_cast<T *>(plan.partial) + warp * D + loff;
+#pragma unroll
+    for (int v = 0; v < V; ++v) __stcg(reinterpret_cast<Vec *>(pp + v * SLAB), acc[v]);
+    __threadfence();
+    const int4 hi = __ldg(plan.hub_info + ci.x);
+    int ticket = 0;
+    if (lane == 0) ticket = atomicAdd(plan.tickets + ci.x, 1);
+    ticket = __shfl_sync(0xffffffffu, ticket, 0);
+    if (ticket != hi.z - 1) return;
+    __threadfence();
+    if (lane == 0) plan.tickets[ci.x] = 0;  // ready for the next launch
+#pragma unroll
+    for (int v = 0; v < V; ++v) vzero(acc[v]);
+    const T *p0 = static_cast<const T *>(plan.partial) + (int64_t)hi.y * D + loff;
+    for (int c = 0; c < hi.z; ++c) {
+#pragma unroll
+      for (int v = 0; v < V; ++v) vadd(acc[v], __ldcg(reinterpret_cast<const Vec *>(p0 + (int64_t)c * D + v * SLAB)));
+    }
+    row = hi.x;
+  } else {
+    row = warp - plan.n_chunks;
+    if (row >= n_rows) return;
+    const int32_t s = rowptr[row], e = rowptr[row + 1];
+    if (e - s > plan.hub_threshold) return;  // a hub: handled by the chunk warps
+    gather_range<T, V, MUL>(col, val, x, mul, s, e, lane, acc);
   }
 
   T *yr = y + row * D + loff;
@@ -189,21 +249,32 @@ spmm_warp_row_generic_kernel(const int32_t *__restrict__ rowptr, const int32_t *
 
 template <typename T, bool MUL, bool ADD>
 static int launch_spmm(const int32_t *rowptr, const int32_t *col, const T *val, int64_t n_rows, int64_t d,
-                       const T *x, const T *mul, const T *e1, const T *e2, T *y, cudaStream_t st) {
+                       const T *x, const T *mul, const T *e1, const T *e2, T *y, SpmmPlan plan, cudaStream_t st) {
   constexpr int SLAB = 32 * VecOf<T>::N;
   const int T_ = 256;
-  const unsigned grid = (unsigned)ceil_div<int64_t>(n_rows * 32, T_);
+  const bool fixed = (d == SLAB || d == 2 * SLAB || d == 4 * SLAB);
+  if (!fixed) {  // unusual widths: no hub splitting (the generic kernel walks every row)
+    plan.hub_threshold = INT32_MAX;
+    plan.n_chunks = 0;
+  }
+  const unsigned grid = (unsigned)ceil_div<int64_t>((n_rows + plan.n_chunks) * 32, T_);
   if (d == SLAB)
-    spmm_warp_row_kernel<T, 1, MUL, ADD><<<grid, T_, 0, st>>>(rowptr, col, val, n_rows, x, mul, e1, e2, y);
+    spmm_warp_row_kernel<T, 1, MUL, ADD><<<grid, T_, 0, st>>>(rowptr, col, val, n_rows, x, mul, e1, e2, y, plan);
   else if (d == 2 * SLAB)
-    spmm_warp_row_kernel<T, 2, MUL, ADD><<<grid, T_, 0, st>>>(rowptr, col, val, n_rows, x, mul, e1, e2, y);
+    spmm_warp_row_kernel<T, 2, MUL, ADD><<<grid, T_, 0, st>>>(rowptr, col, val, n_rows, x, mul, e1, e2, y, plan);
   else if (d == 4 * SLAB)
-    spmm_warp_row_kernel<T, 4, MUL, ADD><<<grid, T_, 0, st>>>(rowptr, col, val, n_rows, x, mul, e1, e2, y);
+    spmm_warp_row_kernel<T, 4, MUL, ADD><<<grid, T_, 0, st>>>(rowptr, col, val, n_rows, x, mul, e1, e2, y, plan);
   else
     spmm_warp_row_generic_kernel<T, MUL, ADD><<<grid, T_, 0, st>>>(rowptr, col, val, n_rows, d, x, mul, e1, e2,
                                                                   y);
   GDR_LAUNCHED();
   return GDR_OK;
+}
+
+static SpmmPlan no_plan() {
+  SpmmPlan p{};
+  p.hub_threshold = INT32_MAX;
+  return p;
 }
 
 }  // namespace gdr
@@ -212,9 +283,11 @@ using namespace gdr;
 
 extern "C" {
 
-int gdr_spmm_csr_f32(const int32_t *rowptr, const int32_t *col, const float *val, int64_t n_rows, int64_t d,
-                     const float *x, const float *mul, const float *e1, const float *e2, float *y,
-                     gdr_stream_t stream) {
+int gdr_spmm_csr_planned_f32(const int32_t *rowptr, const int32_t *col, const float *val, int64_t n_rows,
+                             int64_t d, const float *x, const float *mul, const float *e1, const float *e2,
+                             float *y, int32_t hub_threshold, int64_t n_hubs, const int32_t *hub_info,
+                             int64_t n_chunks, const int32_t *chunk_info, int32_t *tickets, float *partial,
+                             gdr_stream_t stream) {
   GDR_CHECK_ARG(n_rows >= 0 && d > 0, GDR_E_BADARG, "spmm_f32: bad sizes");
   GDR_CHECK_ARG(d % 4 == 0, GDR_E_SHAPE, "spmm_f32: d=%lld must be a multiple of 4", (long long)d);
   GDR_CHECK_ARG(rowptr && x && y, GDR_E_BADARG, "spmm_f32: null pointer");
@@ -222,11 +295,31 @@ int gdr_spmm_csr_f32(const int32_t *rowptr, const int32_t *col, const float *val
   GDR_CHECK_ARG((((uintptr_t)x | (uintptr_t)y | (uintptr_t)mul | (uintptr_t)e1 | (uintptr_t)e2) & 15) == 0,
                 GDR_E_SHAPE, "spmm_f32: pointers must be 16-byte aligned");
   if (n_rows == 0) return GDR_OK;
+  GDR_CHECK_ARG(n_hubs >= 0 && n_chunks >= 0 && n_chunks < (int64_t)INT32_MAX, GDR_E_BADARG,
+                "spmm_f32: bad plan sizes");
+  GDR_CHECK_ARG(n_chunks == 0 || (hub_threshold > 0 && n_hubs > 0 && hub_info && chunk_info && tickets && partial),
+                GDR_E_BADARG, "spmm_f32: incomplete plan");
   cudaStream_t st = as_stream(stream);
-  if (mul && e1) return launch_spmm<float, true, true>(rowptr, col, val, n_rows, d, x, mul, e1, e2, y, st);
-  if (mul) return launch_spmm<float, true, false>(rowptr, col, val, n_rows, d, x, mul, e1, e2, y, st);
-  if (e1) return launch_spmm<float, false, true>(rowptr, col, val, n_rows, d, x, mul, e1, e2, y, st);
-  return launch_spmm<float, false, false>(rowptr, col, val, n_rows, d, x, mul, e1, e2, y, st);
+  SpmmPlan plan = no_plan();
+  if (n_chunks > 0) {
+    plan.hub_threshold = hub_threshold;
+    plan.n_chunks = (int32_t)n_chunks;
+    plan.chunk_info = reinterpret_cast<const int4 *>(chunk_info);
+    plan.hub_info = reinterpret_cast<const int4 *>(hub_info);
+    plan.tickets = tickets;
+    plan.partial = partial;
+  }
+  if (mul && e1) return launch_spmm<float, true, true>(rowptr, col, val, n_rows, d, x, mul, e1, e2, y, plan, st);
+  if (mul) return launch_spmm<float, true, false>(rowptr, col, val, n_rows, d, x, mul, e1, e2, y, plan, st);
+  if (e1) return launch_spmm<float, false, true>(rowptr, col, val, n_rows, d, x, mul, e1, e2, y, plan, st);
+  return launch_spmm<float, false, false>(rowptr, col, val, n_rows, d, x, mul, e1, e2, y, plan, st);
+}
+
+int gdr_spmm_csr_f32(const int32_t *rowptr, const int32_t *col, const float *val, int64_t n_rows, int64_t d,
+                     const float *x, const float *mul, const float *e1, const float *e2, float *y,
+                     gdr_stream_t stream) {
+  return gdr_spmm_csr_planned_f32(rowptr, col, val, n_rows, d, x, mul, e1, e2, y, 0, 0, nullptr, 0, nullptr,
+                                  nullptr, nullptr, stream);
 }
 
 int gdr_spmm_csr_f64(const int32_t *rowptr, const int32_t *col, const double *val, int64_t n_rows, int64_t d,
@@ -237,7 +330,7 @@ int gdr_spmm_csr_f64(const int32_t *rowptr, const int32_t *col, const double *va
   GDR_CHECK_ARG((((uintptr_t)x | (uintptr_t)y) & 15) == 0, GDR_E_SHAPE,
                 "spmm_f64: pointers must be 16-byte aligned");
   if (n_rows == 0) return GDR_OK;
-  return launch_spmm<double, false, false>(rowptr, col, val, n_rows, d, x, nullptr, nullptr, nullptr, y,
+  return launch_spmm<double, false, false>(rowptr, col, val, n_rows, d, x, nullptr, nullptr, nullptr, y, no_plan(),
                                            as_stream(stream));
 }
 

@@ -27,6 +27,7 @@ class DeviceCSR:
         self.n_rows = int(n_rows)
         self.n_cols = int(n_cols)
         self._t = None
+        self._plan = None
 
     # ---- constructors -------------------------------------------------------------------
     @classmethod
@@ -147,6 +148,36 @@ class DeviceCSR:
             return self
         return DeviceCSR(self.rowptr, self.col, self.val.to(dtype), self.n_rows, self.n_cols)
 
+    # ---- degree-aware schedule --------------------------------------------------------------------
+    HUB_THRESHOLD = 512    # rows longer than this are cut into chunks ...
+    HUB_CHUNK = 256        # ... of this many entries, one warp each
+
+    def plan(self):
+        """Hub-row schedule for gdr_spmm_csr_planned_f32, built once per matrix (index arithmetic on the row
+        pointers; see the SpmmPlan comment in csrc/spmm.cu).  None when no row exceeds HUB_THRESHOLD."""
+        if self._plan is None:
+            dev = self.device
+            deg = (self.rowptr[1:] - self.rowptr[:-1]).to(torch.int64)
+            hubs = torch.nonzero(deg > self.HUB_THRESHOLD).flatten()
+            if hubs.numel() == 0:
+                self._plan = False
+            else:
+                nch = (deg[hubs] + self.HUB_CHUNK - 1) // self.HUB_CHUNK
+                first = torch.cumsum(nch, 0) - nch
+                total = int(nch.sum().item())
+                hub_of = torch.repeat_interleave(torch.arange(hubs.numel(), device=dev), nch)
+                k = torch.arange(total, device=dev) - first[hub_of]
+                row_start = self.rowptr[hubs].to(torch.int64)
+                start = row_start[hub_of] + k * self.HUB_CHUNK
+                end = torch.minimum(start + self.HUB_CHUNK, self.rowptr[hubs + 1].to(torch.int64)[hub_of])
+                zc = torch.zeros_like(start)
+                chunk_info = torch.stack([hub_of, start, end, zc], 1).to(torch.int32).contiguous()
+                hub_info = torch.stack([hubs, first, nch, torch.zeros_like(nch)], 1).to(torch.int32).contiguous()
+                tickets = torch.zeros(hubs.numel(), dtype=torch.int32, device=dev)
+                self._plan = dict(n_hubs=int(hubs.numel()), n_chunks=total, hub_info=hub_info,
+                                  chunk_info=chunk_info, tickets=tickets, partial=None)
+        return self._plan or None
+
     # ---- SpMM ------------------------------------------------------------------------------------
     def spmm(self, x, mul=None, e1=None, e2=None, out=None):
         """out = self · x  (gathered operand x ⊙ mul if mul is given; + e1 ⊙ e2 if given)."""
@@ -163,9 +194,19 @@ class DeviceCSR:
             ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             ev0.record()
         if x.dtype == torch.float32:
-            _ffi.check(L.gdr_spmm_csr_f32(_ffi.ptr(self.rowptr), _ffi.ptr(self.col), _ffi.ptr(self.val), self.n_rows,
-                                          d, _ffi.ptr(x), _ffi.ptr(mul), _ffi.ptr(e1), _ffi.ptr(e2), _ffi.ptr(out),
-                                          _ffi.stream()), "spmm_csr_f32")
+            pl = self.plan()
+            if pl is None:
+                _ffi.check(L.gdr_spmm_csr_f32(_ffi.ptr(self.rowptr), _ffi.ptr(self.col), _ffi.ptr(self.val),
+                                              self.n_rows, d, _ffi.ptr(x), _ffi.ptr(mul), _ffi.ptr(e1), _ffi.ptr(e2),
+                                              _ffi.ptr(out), _ffi.stream()), "spmm_csr_f32")
+            else:
+                if pl["partial"] is None or pl["partial"].shape[1] != d:
+                    pl["partial"] = torch.empty(pl["n_chunks"], d, dtype=torch.float32, device=x.device)
+                _ffi.check(L.gdr_spmm_csr_planned_f32(
+                    _ffi.ptr(self.rowptr), _ffi.ptr(self.col), _ffi.ptr(self.val), self.n_rows, d, _ffi.ptr(x),
+                    _ffi.ptr(mul), _ffi.ptr(e1), _ffi.ptr(e2), _ffi.ptr(out), self.HUB_THRESHOLD, pl["n_hubs"],
+                    _ffi.ptr(pl["hub_info"]), pl["n_chunks"], _ffi.ptr(pl["chunk_info"]), _ffi.ptr(pl["tickets"]),
+                    _ffi.ptr(pl["partial"]), _ffi.stream()), "spmm_csr_planned_f32")
         elif x.dtype == torch.float64:
             if mul is not None or e1 is not None:
                 raise RuntimeError("spmm: fused operands are fp32-only")

@@ -91,6 +91,18 @@ int gdr_csr_normalize_f64(const int32_t *rowptr, const int32_t *col, const doubl
 int gdr_spmm_csr_f32(const int32_t *rowptr, const int32_t *col, const float *val,
                      int64_t n_rows, int64_t d, const float *x, const float *mul,
                      const float *e1, const float *e2, float *y, gdr_stream_t stream);
+/* Same product with a degree-aware schedule (the "plan"): rows with more than hub_threshold entries
+ * are cut into chunks; chunk_info[c] = {hub index, first entry, end entry, 0} and
+ * hub_info[h] = {row, first chunk, #chunks, 0} (int32 x4 each, 16-byte aligned).  One warp reduces one
+ * chunk into partial[c][0..d) and the last warp of a hub (tickets[h], zero on entry, reset on exit)
+ * adds the partials in chunk order, so results are independent of scheduling.  n_chunks == 0 means
+ * "no hubs" and is what gdr_spmm_csr_f32 passes.  partial: fp32 [n_chunks, d], caller-owned.        */
+int gdr_spmm_csr_planned_f32(const int32_t *rowptr, const int32_t *col, const float *val,
+                             int64_t n_rows, int64_t d, const float *x, const float *mul,
+                             const float *e1, const float *e2, float *y, int32_t hub_threshold,
+                             int64_t n_hubs, const int32_t *hub_info, int64_t n_chunks,
+                             const int32_t *chunk_info, int32_t *tickets, float *partial,
+                             gdr_stream_t stream);
 int gdr_spmm_csr_f64(const int32_t *rowptr, const int32_t *col, const double *val,
                      int64_t n_rows, int64_t d, const double *x, double *y,
                      gdr_stream_t stream);
