@@ -51,6 +51,11 @@ def parse_args():
     p.add_argument("--rmat-d", type=int, default=128)
     p.add_argument("--no-rmat", action="store_true", help="skip the secondary R-MAT SpMM measurement at N=1")
     p.add_argument("--no-cpu-baseline", action="store_true")
+    p.add_argument("--no-overlap", action="store_true", help="N>1: exchange first, then one local SpMM")
+    p.add_argument("--diag", action="store_true", help="N>1: print per-rank timings of the step's parts to stderr")
+    p.add_argument("--row-weight", type=float, default=6.0,
+                   help="partition balance: cost(row) = nnz(row) + row_weight; 6 = measured per-row overhead of the "
+                        "SpMM kernel in edge-equivalents (DESIGN.md, multi-GPU)")
     p.add_argument("--cpu-iters", type=int, default=3, help="iterations of the CPU baseline sample")
     return p.parse_args()
 
@@ -372,14 +377,6 @@ def run_rmat_spmm_single(args, steps, warmup):
             "l2": "inputs larger than L2 (X = %.1f GB)" % (n * d * 4 / 1e9)}
 
 
-def nnz_balanced_bounds(rowptr_cpu, parts):
-    """Contiguous row blocks with ~equal nnz (R-MAT is skewed: equal row counts would not balance)."""
-    nnz = int(rowptr_cpu[-1])
-    targets = (np.arange(1, parts) * (nnz / parts)).astype(np.int64)
-    cuts = np.searchsorted(rowptr_cpu, targets, side="left")
-    return np.concatenate([[0], cuts, [len(rowptr_cpu) - 1]]).astype(np.int64)
-
-
 def run_rmat_spmm_dist(args):
     """Row-partitioned SpMM: rank r owns rows [lo_r, hi_r) of Â (nnz-balanced) and the matching rows of X
     and Y.  One step = all-gather of the X blocks over NCCL/NVLink + the local SpMM (dist.py)."""
@@ -395,19 +392,49 @@ def run_rmat_spmm_dist(args):
     dist.init_process_group("nccl", device_id=dev)
     full = build_rmat_csr(args.rmat_scale, args.rmat_edge_factor, dev)        # same seed on every rank
     n, d, nnz_total = full.n_rows, args.rmat_d, full.nnz
-    bounds = nnz_balanced_bounds(full.rowptr.cpu().numpy(), world)
-    part = gdist.RowPartitionedSpMM.from_full(full, bounds, rank, world, d)
-    del full
-    torch.cuda.empty_cache()
+    rp = full.rowptr.cpu().numpy().astype(np.int64)
+    bounds = gdist.nnz_balanced_bounds(rp + (np.arange(len(rp)) * args.row_weight).astype(np.int64), world)
     lo, hi = int(bounds[rank]), int(bounds[rank + 1])
     gen = torch.Generator(device=dev).manual_seed(2)
     x_full = torch.randn(n, d, device=dev, generator=gen)                     # identical on every rank
-    x_local = x_full[lo:hi].clone()
+    y_ref = full.spmm(x_full)[lo:hi].clone()                                  # 1-GPU product, for the check below
+    part = gdist.RowPartitionedSpMM.from_full(full, bounds, rank, world, d, overlap=not args.no_overlap)
+    del full
+    part.x_own.copy_(x_full[lo:hi])
     del x_full
+    torch.cuda.empty_cache()
+    x_local = None
+    y = part.spmm(x_local)
+    err = (y - y_ref).abs()
+    tol_ok = bool(((err <= 1e-6) | (err <= 1e-5 * y_ref.abs()) | (err <= 4e-7 * y_ref.abs().max())).all().item())
+    max_err = float(err.max().item())
+    del y_ref, err
     for _ in range(args.warmup):
         part.spmm(x_local)
     torch.cuda.synchronize()
     dist.barrier()
+    if args.diag:
+        def timed(fn, reps=5):
+            torch.cuda.synchronize()
+            dist.barrier()
+            a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a_.record()
+            for _ in range(reps):
+                fn()
+            b_.record()
+            torch.cuda.synchronize()
+            return a_.elapsed_time(b_) / reps
+        t_ex = timed(part._exchange)
+        if part.overlap:
+            t_own = timed(lambda: part.csr_own.spmm(part.xbuf, out=part.y))
+            t_rem = timed(lambda: part.csr_rem.spmm(part.xbuf, e1=part.y, out=part.y))
+            extra = "own %.2f ms (nnz %d) rem %.2f ms (nnz %d)" % (t_own, part.csr_own.nnz, t_rem, part.csr_rem.nnz)
+        else:
+            t_all = timed(lambda: part.csr_all.spmm(part.xbuf, out=part.y))
+            extra = "local spmm %.2f ms (nnz %d)" % (t_all, part.csr_all.nnz)
+        sys.stderr.write("[diag] rank %d rows %d recv_rows %d send_rows %d exchange %.2f ms %s\n" % (
+            rank, hi - lo, part.recv_rows, int(part.send_idx.numel()), t_ex, extra))
+        sys.stderr.flush()
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
@@ -439,12 +466,15 @@ def run_rmat_spmm_dist(args):
                                    "all-gather of X blocks + local SpMM per step (BASELINE configs[4])"
                                    % (args.rmat_scale, args.rmat_edge_factor, d),
                        "nodes": n, "nnz": nnz_total, "d": d, "parallelism": f"row-partition x{world}",
-                       "l2": "inputs larger than L2", "transport": part.transport},
+                       "l2": "inputs larger than L2", "transport": part.transport,
+                       "rows_received_per_rank_rank0": part.recv_rows,
+                       "check_vs_1gpu_product": {"within_tolerance": tol_ok, "max_abs_err": max_err}},
             "e2e": None, "gpu_launches": int(launches.item()), "clocks": clk,
             "roofline": {"kernel": "spmm_warp_row_kernel<float> + all-gather", "bound": "hbm",
                          "achieved": gbs, "peak": peak * world, "unit": "GB/s", "frac": gbs / (peak * world),
                          "traffic": None, "peak_source": peak_src + f" x{world} GPUs",
-                         "allgather_bytes_in_per_rank": int((n - (hi - lo)) * d * 4)},
+                         "exchange_bytes_in_rank0": int(part.recv_rows * d * 4),
+                         "allgather_bytes_in_would_be": int((n - (hi - lo)) * d * 4)},
         }
     dist.destroy_process_group()
     return line

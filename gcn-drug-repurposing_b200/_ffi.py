@@ -48,6 +48,7 @@ _SIGNATURES = {
     "gdr_gss_loss_workspace_bytes": (c_i64, [c_i64, c_i64]),
     "gdr_gss_loss_fwd_bwd_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_f32, c_f32, c_ptr, c_ptr, c_ptr,
                                          c_i64, c_ptr]),
+    "gdr_gather_rows_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr]),
     "gdr_scatter_rows_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr]),
     "gdr_gram_percentile_workspace_bytes": (c_i64, [c_i64, c_i64]),
     "gdr_gram_percentile_f32": (c_i32, [c_ptr, c_i64, c_i64, c_f64, ctypes.POINTER(c_f32), c_ptr, c_i64, c_ptr]),

@@ -134,6 +134,16 @@ int gdr_gss_loss_fwd_bwd_f32(const float *embs, const int64_t *index, int64_t b,
   return GDR_OK;
 }
 
+int gdr_gather_rows_f32(const float *src, const int64_t *index, int64_t b, int64_t n, int64_t d, float *dst,
+                        gdr_stream_t stream) {
+  GDR_CHECK_ARG(b >= 0 && n >= 0 && d > 0 && d % 4 == 0, GDR_E_BADARG, "gather_rows: bad sizes");
+  if (b == 0) return GDR_OK;
+  GDR_CHECK_ARG(src && dst, GDR_E_BADARG, "gather_rows: null pointer");
+  gather_rows_kernel<<<(unsigned)ceil_div<int64_t>(b * 32, 256), 256, 0, as_stream(stream)>>>(src, index, b, n, d, dst);
+  GDR_LAUNCHED();
+  return GDR_OK;
+}
+
 int gdr_scatter_rows_f32(const float *ge, const int64_t *index, int64_t b, int64_t n, int64_t d,
                          const float *scale_dev, float *gh, gdr_stream_t stream) {
   GDR_CHECK_ARG(b >= 0 && d > 0 && ge && gh, GDR_E_BADARG, "scatter_rows: bad args");

@@ -143,8 +143,8 @@ template <typename T, int V, bool MUL, bool ADD>
 __global__ void __launch_bounds__(256)
 spmm_warp_row_kernel(const int32_t *__restrict__ rowptr, const int32_t *__restrict__ col,
                      const T *__restrict__ val, int64_t n_rows, const T *__restrict__ x,
-                     const T *__restrict__ mul, const T *__restrict__ e1, const T *__restrict__ e2,
-                     T *__restrict__ y, const SpmmPlan plan) {
+                     const T *__restrict__ mul, const T *e1, const T *__restrict__ e2, T *y,
+                     const SpmmPlan plan) {
   using Vec = typename VecOf<T>::type;
   constexpr int EPL = VecOf<T>::N;      // elements per 16-byte lane load
   constexpr int SLAB = 32 * EPL;        // elements per warp-wide load
@@ -194,8 +194,8 @@ spmm_warp_row_kernel(const int32_t *__restrict__ rowptr, const int32_t *__restri
   for (int v = 0; v < V; ++v) {
     if (ADD) {
       Vec a = vload<T>(e1 + row * D + loff + v * SLAB);
-      Vec b = vload<T>(e2 + row * D + loff + v * SLAB);
-      vadd(acc[v], vmul(a, b));
+      if (e2 != nullptr) a = vmul(a, vload<T>(e2 + row * D + loff + v * SLAB));
+      vadd(acc[v], a);
     }
     *reinterpret_cast<Vec *>(yr + v * SLAB) = acc[v];
   }
@@ -241,7 +241,11 @@ spmm_warp_row_generic_kernel(const int32_t *__restrict__ rowptr, const int32_t *
       }
     }
     if (live) {
-      if (ADD) vadd(acc, vmul(vload<T>(e1 + row * d + cc), vload<T>(e2 + row * d + cc)));
+      if (ADD) {
+        Vec a = vload<T>(e1 + row * d + cc);
+        if (e2 != nullptr) a = vmul(a, vload<T>(e2 + row * d + cc));
+        vadd(acc, a);
+      }
       *reinterpret_cast<Vec *>(y + row * d + cc) = acc;
     }
   }
@@ -291,7 +295,7 @@ int gdr_spmm_csr_planned_f32(const int32_t *rowptr, const int32_t *col, const fl
   GDR_CHECK_ARG(n_rows >= 0 && d > 0, GDR_E_BADARG, "spmm_f32: bad sizes");
   GDR_CHECK_ARG(d % 4 == 0, GDR_E_SHAPE, "spmm_f32: d=%lld must be a multiple of 4", (long long)d);
   GDR_CHECK_ARG(rowptr && x && y, GDR_E_BADARG, "spmm_f32: null pointer");
-  GDR_CHECK_ARG((e1 == nullptr) == (e2 == nullptr), GDR_E_BADARG, "spmm_f32: e1/e2 must come together");
+  GDR_CHECK_ARG(e1 != nullptr || e2 == nullptr, GDR_E_BADARG, "spmm_f32: e2 needs e1");
   GDR_CHECK_ARG((((uintptr_t)x | (uintptr_t)y | (uintptr_t)mul | (uintptr_t)e1 | (uintptr_t)e2) & 15) == 0,
                 GDR_E_SHAPE, "spmm_f32: pointers must be 16-byte aligned");
   if (n_rows == 0) return GDR_OK;

@@ -85,7 +85,8 @@ int gdr_csr_normalize_f64(const int32_t *rowptr, const int32_t *col, const doubl
  * replaces torch.sparse.mm (modules/model.py:163,169), its autograd Âᵀ·G (pass the
  * transposed CSR) and scipy's x*M (multiscale/diff_prof/diffusion_profiles.py:85).
  *   Y[r,:] = sum_e val[e] * X[col[e],:] (* P[col[e],:] if mul != NULL)
- *            (+ E1[r,:] * E2[r,:]       if e1 != NULL)
+ *            (+ E1[r,:] * E2[r,:]       if e1 != NULL; e2 == NULL means + E1[r,:], and e1 may be y itself:
+ *                                        in-place accumulation  Y += Â·X  for column-split operands)
  * mul: the reference's torch.mul(Ax, features) (model.py:168) folded into the gather.
  * e1,e2: the backward's element-wise addend  dX = Âᵀ·dP + dR ⊙ P.                     */
 int gdr_spmm_csr_f32(const int32_t *rowptr, const int32_t *col, const float *val,
@@ -152,6 +153,9 @@ int gdr_gss_loss_fwd_bwd_f32(const float *embs, const int64_t *index, int64_t b,
                              int64_t n, int64_t d, float alpha, float beta,
                              float *loss_out, float *grad_e_out, void *workspace,
                              int64_t workspace_bytes, gdr_stream_t stream);
+/* dst[i,:] = src[index[i],:]  (embs[index], model.py:216; also the send-buffer pack of the partitioned SpMM) */
+int gdr_gather_rows_f32(const float *src, const int64_t *index, int64_t b, int64_t n, int64_t d,
+                        float *dst, gdr_stream_t stream);
 /* gh[index[i],:] += scale_dev[0] * ge[i,:]  (autograd of embs[index]); gh pre-zeroed. */
 int gdr_scatter_rows_f32(const float *ge, const int64_t *index, int64_t b, int64_t n,
                          int64_t d, const float *scale_dev, float *gh, gdr_stream_t stream);
