@@ -52,6 +52,10 @@ def parse_args():
     p.add_argument("--no-rmat", action="store_true", help="skip the secondary R-MAT SpMM measurement at N=1")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-overlap", action="store_true", help="N>1: exchange first, then one local SpMM")
+    p.add_argument("--two-comms", action="store_true", help="N>1, lshape: partial rows on a second NCCL communicator")
+    p.add_argument("--partition", choices=["lshape", "rows"], default="lshape",
+                   help="N>1: L-shaped partition (blocks above the diagonal are multiplied at the column owner and "
+                        "their partial rows sent back) or plain row blocks with a pull exchange")
     p.add_argument("--diag", action="store_true", help="N>1: print per-rank timings of the step's parts to stderr")
     p.add_argument("--row-weight", type=float, default=6.0,
                    help="partition balance: cost(row) = nnz(row) + row_weight; 6 = measured per-row overhead of the "
@@ -389,16 +393,40 @@ def run_rmat_spmm_dist(args):
     local = int(os.environ.get("LOCAL_RANK", rank))
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
-    dist.init_process_group("nccl", device_id=dev)
+    opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)        # exchanges overtake queued SpMM CTAs
+    import datetime
+    dist.init_process_group("nccl", device_id=dev, pg_options=opts, timeout=datetime.timedelta(seconds=180))
     full = build_rmat_csr(args.rmat_scale, args.rmat_edge_factor, dev)        # same seed on every rank
     n, d, nnz_total = full.n_rows, args.rmat_d, full.nnz
-    rp = full.rowptr.cpu().numpy().astype(np.int64)
-    bounds = gdist.nnz_balanced_bounds(rp + (np.arange(len(rp)) * args.row_weight).astype(np.int64), world)
+    if args.partition == "lshape":
+        deg = (full.rowptr[1:] - full.rowptr[:-1]).to(torch.int64)
+        row_of = torch.repeat_interleave(torch.arange(n, device=dev), deg)
+        hist, bin_size = gdist.coarse_histogram(row_of, full.col.to(torch.int64), n, min(1024, n))
+        del row_of, deg
+        bounds = gdist.lshape_bounds(hist.cpu().numpy(), bin_size, n, world, row_weight=args.row_weight)
+    else:
+        rp = full.rowptr.cpu().numpy().astype(np.int64)
+        bounds = gdist.nnz_balanced_bounds(rp + (np.arange(len(rp)) * args.row_weight).astype(np.int64), world)
     lo, hi = int(bounds[rank]), int(bounds[rank + 1])
     gen = torch.Generator(device=dev).manual_seed(2)
     x_full = torch.randn(n, d, device=dev, generator=gen)                     # identical on every rank
-    y_ref = full.spmm(x_full)[lo:hi].clone()                                  # 1-GPU product, for the check below
-    part = gdist.RowPartitionedSpMM.from_full(full, bounds, rank, world, d, overlap=not args.no_overlap)
+    y_full = full.spmm(x_full)
+    y_ref = y_full[lo:hi].clone()                                             # 1-GPU product, for the check below
+    t1a, t1b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    t1a.record()
+    for _ in range(3):
+        full.spmm(x_full, out=y_full)                                         # the same product on ONE GPU, timed
+    t1b.record()
+    torch.cuda.synchronize()
+    ms_1gpu = t1a.elapsed_time(t1b) / 3
+    del y_full
+    if args.partition == "lshape":
+        g2 = dist.new_group(backend="nccl", pg_options=dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)) \
+            if args.two_comms else None
+        part = gdist.LShapedSpMM.from_full(full, bounds, rank, world, d, group_partials=g2)
+    else:
+        part = gdist.RowPartitionedSpMM.from_full(full, bounds, rank, world, d, overlap=not args.no_overlap)
     del full
     part.x_own.copy_(x_full[lo:hi])
     del x_full
@@ -424,17 +452,34 @@ def run_rmat_spmm_dist(args):
             b_.record()
             torch.cuda.synchronize()
             return a_.elapsed_time(b_) / reps
-        t_ex = timed(part._exchange)
-        if part.overlap:
+        if args.partition == "lshape":
+            t_x = timed(part.exchange_x)
+            nop = lambda: None                     # every rank must enter timed() (it holds a barrier)
+            t_push = timed((lambda: part.push.spmm(part.x_own, out=part.psend)) if part.n_psend else nop)
+            t_p = timed(part.exchange_partials)
+            t_pull = timed(lambda: part.pull.spmm(part.xbuf, out=part.y))
+            t_add = timed((lambda: part.add.spmm(part.precv, e1=part.y, out=part.y)) if part.n_precv else nop)
+            t_all = timed(lambda: part.spmm(None))
+            sys.stderr.write("[diag] rank %d rows %d | x-exchange %.2f ms (recv %d send %d rows) | push %.2f ms (nnz %d, "
+                             "%d rows) | partial-exchange %.2f ms (recv %d) | pull %.2f ms (nnz %d) | add %.2f ms | "
+                             "step %.2f ms\n" % (rank, hi - lo, t_x, sum(part.xrecv_splits), int(part.send_idx.numel()),
+                                                 t_push, part.push.nnz, part.n_psend, t_p, part.n_precv, t_pull,
+                                                 part.pull.nnz, t_add, t_all))
+            sys.stderr.flush()
+        t_ex = 0.0 if args.partition == "lshape" else timed(part._exchange)
+        if args.partition == "lshape":
+            extra = ""
+        elif part.overlap:
             t_own = timed(lambda: part.csr_own.spmm(part.xbuf, out=part.y))
             t_rem = timed(lambda: part.csr_rem.spmm(part.xbuf, e1=part.y, out=part.y))
             extra = "own %.2f ms (nnz %d) rem %.2f ms (nnz %d)" % (t_own, part.csr_own.nnz, t_rem, part.csr_rem.nnz)
         else:
             t_all = timed(lambda: part.csr_all.spmm(part.xbuf, out=part.y))
             extra = "local spmm %.2f ms (nnz %d)" % (t_all, part.csr_all.nnz)
-        sys.stderr.write("[diag] rank %d rows %d recv_rows %d send_rows %d exchange %.2f ms %s\n" % (
-            rank, hi - lo, part.recv_rows, int(part.send_idx.numel()), t_ex, extra))
-        sys.stderr.flush()
+        if args.partition != "lshape":
+            sys.stderr.write("[diag] rank %d rows %d recv_rows %d send_rows %d exchange %.2f ms %s\n" % (
+                rank, hi - lo, part.recv_rows, int(part.send_idx.numel()), t_ex, extra))
+            sys.stderr.flush()
     clocks = ClockSampler(local)
     if rank == 0:
         clocks.start()
@@ -462,10 +507,13 @@ def run_rmat_spmm_dist(args):
             "metric": "spmm_gedges_per_s", "value": nnz_total / (ms * 1e-3) / 1e9, "unit": "GEdges/s",
             "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms,
             "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": "rmat_spmm: Y = A_hat X, R-MAT scale %d edge-factor %d d %d, rows partitioned by nnz, "
-                                   "all-gather of X blocks + local SpMM per step (BASELINE configs[4])"
+            "config": {"workload": "rmat_spmm: Y = A_hat X, R-MAT scale %d edge-factor %d d %d, rows partitioned over the GPUs, "
+                                   "exchange of the referenced X rows / partial Y rows + local SpMM per step "
+                                   "(BASELINE configs[4])"
                                    % (args.rmat_scale, args.rmat_edge_factor, d),
-                       "nodes": n, "nnz": nnz_total, "d": d, "parallelism": f"row-partition x{world}",
+                       "nodes": n, "nnz": nnz_total, "d": d,
+                       "parallelism": f"{'L-shaped' if args.partition == 'lshape' else 'row'}-partition x{world}",
+                       "same_product_on_1_gpu_ms": ms_1gpu, "bounds": [int(b) for b in bounds],
                        "l2": "inputs larger than L2", "transport": part.transport,
                        "rows_received_per_rank_rank0": part.recv_rows,
                        "check_vs_1gpu_product": {"within_tolerance": tol_ok, "max_abs_err": max_err}},

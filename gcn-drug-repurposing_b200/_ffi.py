@@ -48,6 +48,15 @@ _SIGNATURES = {
     "gdr_gss_loss_workspace_bytes": (c_i64, [c_i64, c_i64]),
     "gdr_gss_loss_fwd_bwd_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_f32, c_f32, c_ptr, c_ptr, c_ptr,
                                          c_i64, c_ptr]),
+    "gdr_gemm_nt_tc_workspace_bytes": (c_i64, [c_i64, c_i64, c_i64]),
+    "gdr_gemm_nt_tc_f32": (c_i32, [c_ptr, c_i64, c_ptr, c_i64, c_i64, c_i64, c_i64, c_ptr, c_i64, c_ptr, c_i64, c_ptr]),
+    "gdr_gcn_layer_fwd_tc_workspace_bytes": (c_i64, [c_i64, c_i64]),
+    "gdr_gcn_layer_fwd_tc_f32": (c_i32, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_f32, c_i64, c_i64, c_ptr,
+                                         c_ptr, c_ptr, c_i64, c_ptr]),
+    "gdr_linear_bwd_input_tc_workspace_bytes": (c_i64, [c_i64, c_i64]),
+    "gdr_linear_bwd_input_tc_f32": (c_i32, [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_i64, c_ptr]),
+    "gdr_linear_bwd_weight_tc_workspace_bytes": (c_i64, [c_i64, c_i64]),
+    "gdr_linear_bwd_weight_tc_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i64, c_i32, c_ptr, c_ptr, c_ptr, c_i64, c_ptr]),
     "gdr_gather_rows_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr]),
     "gdr_scatter_rows_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr]),
     "gdr_gram_percentile_workspace_bytes": (c_i64, [c_i64, c_i64]),

@@ -1,7 +1,7 @@
 // dense.cu — the dense half of GSS_GNNLayer / ResidualGraphConvolutionalNetwork:
 // fused layer transform (two Linear + bias + ELU + residual), row normalisation and the
 // backward pieces autograd derives for them.  Reference: modules/model.py:163-175,197-207.
-#include "gemm_simt.cuh"
+#include "gemm_tc.cuh"
 
 namespace gdr {
 
@@ -227,6 +227,121 @@ int gdr_linear_bwd_weight_f32(const float *g, const float *a, int64_t n, int64_t
   dim3 grid((unsigned)ceil_div<int64_t>(d, GBN), (unsigned)ceil_div<int64_t>(d, GBM), (unsigned)splits);
   gemm_f32_kernel<false, false, EPI_SPLITK><<<grid, GTHREADS, 0, st>>>(q);
   GDR_LAUNCHED();
+  splitk_reduce_kernel<<<(unsigned)ceil_div<int64_t>(d * d, 256), 256, 0, st>>>(part, splits, d * d, accumulate, dw);
+  GDR_LAUNCHED();
+  if (db) {
+    colsum_partial_kernel<<<(unsigned)cs_blocks, 256, 0, st>>>(g, n, d, cpart);
+    GDR_LAUNCHED();
+    splitk_reduce_kernel<<<(unsigned)ceil_div<int64_t>(d, 256), 256, 0, st>>>(cpart, (int)cs_blocks, d, accumulate,
+                                                                             db);
+    GDR_LAUNCHED();
+  }
+  return GDR_OK;
+}
+
+// ---- tcgen05 (3xTF32) variants of the three contractions: same arithmetic contract, operands split into
+// TF32 hi/lo pairs in a caller-owned workspace first (gemm_tc.cu) ------------------------------------------
+
+int64_t gdr_gcn_layer_fwd_tc_workspace_bytes(int64_t n, int64_t d) {
+  if (n < 0 || d <= 0) return GDR_E_BADARG;
+  return 2 * align_up(n * 2 * d * 4, 256) + 2 * align_up(d * 2 * d * 4, 256) + 1024;
+}
+
+int gdr_gcn_layer_fwd_tc_f32(const float *p, const float *t, const float *w1, const float *b1, const float *w2,
+                             const float *b2, const float *residual, float decay, int64_t n, int64_t d, float *z_out,
+                             float *xnext_out, void *workspace, int64_t workspace_bytes, gdr_stream_t stream) {
+  GDR_CHECK_ARG(n >= 0 && d > 0, GDR_E_BADARG, "gcn_layer_fwd_tc: bad sizes");
+  GDR_CHECK_ARG(d % 4 == 0, GDR_E_SHAPE, "gcn_layer_fwd_tc: d=%lld must be a multiple of 4", (long long)d);
+  GDR_CHECK_ARG(p && t && w1 && b1 && w2 && b2 && z_out && xnext_out && workspace, GDR_E_BADARG,
+                "gcn_layer_fwd_tc: null pointer");
+  GDR_CHECK_ARG(workspace_bytes >= gdr_gcn_layer_fwd_tc_workspace_bytes(n, d), GDR_E_WORKSPACE,
+                "gcn_layer_fwd_tc: workspace too small");
+  if (n == 0) return GDR_OK;
+  cudaStream_t st = as_stream(stream);
+  Carver cv(workspace);
+  float *ahi = cv.take<float>(n * 2 * d), *alo = cv.take<float>(n * 2 * d);
+  float *bhi = cv.take<float>(d * 2 * d), *blo = cv.take<float>(d * 2 * d);
+  int rc;
+  if ((rc = tc_split(p, d, d, t, d, d, n, ahi, alo, st))) return rc;      // A = [P | T]   (n x 2d)
+  if ((rc = tc_split(w1, d, d, w2, d, d, d, bhi, blo, st))) return rc;    // B = [W1 | W2] (d x 2d)
+  GemmParams g{};
+  g.c = z_out; g.ldc = d;
+  g.bias1 = b1; g.bias2 = b2; g.residual = residual; g.decay = decay; g.xnext = xnext_out;
+  return tc_gemm(EPI_LAYER, ahi, alo, bhi, blo, n, d, 2 * d, 2 * d, 2 * d, 2 * d, 1, g, st);
+}
+
+int64_t gdr_linear_bwd_input_tc_workspace_bytes(int64_t n, int64_t d) {
+  if (n < 0 || d <= 0) return GDR_E_BADARG;
+  return 2 * align_up(n * d * 4, 256) + 2 * align_up(d * d * 4, 256) + 1024;
+}
+
+int gdr_linear_bwd_input_tc_f32(const float *g, const float *w, const float *e1, const float *e2, int64_t n, int64_t d,
+                                float *c_out, void *workspace, int64_t workspace_bytes, gdr_stream_t stream) {
+  GDR_CHECK_ARG(n >= 0 && d > 0 && g && w && c_out && workspace, GDR_E_BADARG, "linear_bwd_input_tc: bad args");
+  GDR_CHECK_ARG(d % 4 == 0, GDR_E_SHAPE, "linear_bwd_input_tc: d must be a multiple of 4");
+  GDR_CHECK_ARG((e1 == nullptr) == (e2 == nullptr), GDR_E_BADARG, "linear_bwd_input_tc: e1/e2 must come together");
+  GDR_CHECK_ARG(workspace_bytes >= gdr_linear_bwd_input_tc_workspace_bytes(n, d), GDR_E_WORKSPACE,
+                "linear_bwd_input_tc: workspace too small");
+  if (n == 0) return GDR_OK;
+  cudaStream_t st = as_stream(stream);
+  Carver cv(workspace);
+  float *ahi = cv.take<float>(n * d), *alo = cv.take<float>(n * d);
+  float *bhi = cv.take<float>(d * d), *blo = cv.take<float>(d * d);
+  int rc;
+  if ((rc = tc_split(g, d, d, nullptr, 0, 0, n, ahi, alo, st))) return rc;   // A(m=node, k=out) = G
+  if ((rc = tc_split_transpose(w, d, d, d, d, bhi, blo, st))) return rc;     // B(n=in, k=out)  = Wᵀ
+  GemmParams q{};
+  q.c = c_out; q.ldc = d; q.e1 = e1; q.e2 = e2;
+  return tc_gemm(EPI_STORE, ahi, alo, bhi, blo, n, d, d, d, d, d, 1, q, st);
+}
+
+static int tc_splits_for(int64_t n, int64_t d, int64_t *k_per_split) {
+  const int64_t tiles = ceil_div<int64_t>(d, 128) * ceil_div<int64_t>(d, 128);
+  int64_t s = ceil_div<int64_t>(2 * kNumSMs, tiles);                  // ~2 CTAs per SM in total
+  int64_t per = align_up(ceil_div<int64_t>(n > 0 ? n : 1, s), TC_K_ALIGN);
+  if (per < 4 * TC_K_ALIGN) per = 4 * TC_K_ALIGN;                     // at least 4 k-blocks per CTA
+  *k_per_split = per;
+  return (int)ceil_div<int64_t>(n > 0 ? n : 1, per);
+}
+
+int64_t gdr_linear_bwd_weight_tc_workspace_bytes(int64_t n, int64_t d) {
+  if (n < 0 || d <= 0) return GDR_E_BADARG;
+  int64_t per;
+  const int64_t splits = tc_splits_for(n, d, &per);
+  const int64_t ldt = align_up(n > 0 ? n : 1, 4);
+  const int64_t cs_blocks = ceil_div<int64_t>(n > 0 ? n : 1, CS_ROWS);
+  return 4 * align_up(d * ldt * 4, 256) + align_up(splits * d * d * 4, 256) + align_up(cs_blocks * d * 4, 256) + 1024;
+}
+
+int gdr_linear_bwd_weight_tc_f32(const float *g, const float *a, int64_t n, int64_t d, int accumulate, float *dw,
+                                 float *db, void *workspace, int64_t workspace_bytes, gdr_stream_t stream) {
+  GDR_CHECK_ARG(n >= 0 && d > 0 && g && a && dw && workspace, GDR_E_BADARG, "linear_bwd_weight_tc: bad args");
+  GDR_CHECK_ARG(d % 4 == 0, GDR_E_SHAPE, "linear_bwd_weight_tc: d must be a multiple of 4");
+  GDR_CHECK_ARG(workspace_bytes >= gdr_linear_bwd_weight_tc_workspace_bytes(n, d), GDR_E_WORKSPACE,
+                "linear_bwd_weight_tc: workspace too small");
+  cudaStream_t st = as_stream(stream);
+  if (n == 0) {
+    if (!accumulate) {
+      GDR_CUDA(cudaMemsetAsync(dw, 0, d * d * 4, st));
+      if (db) GDR_CUDA(cudaMemsetAsync(db, 0, d * 4, st));
+    }
+    return GDR_OK;
+  }
+  int64_t per;
+  const int splits = tc_splits_for(n, d, &per);
+  const int64_t ldt = align_up(n, 4);
+  const int64_t cs_blocks = ceil_div<int64_t>(n, CS_ROWS);
+  Carver cv(workspace);
+  float *ghi = cv.take<float>(d * ldt), *glo = cv.take<float>(d * ldt);
+  float *ahi = cv.take<float>(d * ldt), *alo = cv.take<float>(d * ldt);
+  float *part = cv.take<float>((int64_t)splits * d * d);
+  float *cpart = cv.take<float>(cs_blocks * d);
+  int rc;
+  if ((rc = tc_split_transpose(g, d, n, d, ldt, ghi, glo, st))) return rc;   // A(m=out, k=node) = Gᵀ
+  if ((rc = tc_split_transpose(a, d, n, d, ldt, ahi, alo, st))) return rc;   // B(n=in,  k=node) = Aᵀ
+  GemmParams q{};
+  q.c = part; q.ldc = d;
+  if ((rc = tc_gemm(EPI_SPLITK, ghi, glo, ahi, alo, d, d, n, ldt, ldt, per, splits, q, st))) return rc;
   splitk_reduce_kernel<<<(unsigned)ceil_div<int64_t>(d * d, 256), 256, 0, st>>>(part, splits, d * d, accumulate, dw);
   GDR_LAUNCHED();
   if (db) {

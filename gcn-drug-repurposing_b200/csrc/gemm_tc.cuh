@@ -1,0 +1,21 @@
+// gemm_tc.cuh — host entry points of the tcgen05 3xTF32 GEMM (gemm_tc.cu) for the other translation units.
+#pragma once
+#include "gemm_simt.cuh"
+
+namespace gdr {
+
+// hi = rn_tf32(x), lo = rn_tf32(x - hi) of [rows, k0 + k1] built from two row-major sources side by side
+// (k1 = 0: one source).  k0, k1 multiples of 4.
+int tc_split(const float *s0, int64_t ld0, int64_t k0, const float *s1, int64_t ld1, int64_t k1, int64_t rows,
+             float *hi, float *lo, cudaStream_t st);
+// the same for the transpose of s[rows, cols]: out[cols, ld_out], columns >= rows zero-filled
+int tc_split_transpose(const float *s, int64_t ld, int64_t rows, int64_t cols, int64_t ld_out, float *hi, float *lo,
+                       cudaStream_t st);
+// C[m,n] = A[m,k]·B[n,k]ᵀ from pre-split operands; `epi` is a GemmEpi, `g` carries the epilogue operands
+int tc_gemm(int epi, const float *ahi, const float *alo, const float *bhi, const float *blo, int64_t m, int64_t n,
+            int64_t k, int64_t lda, int64_t ldb, int64_t k_per_split, int splits, const GemmParams &g,
+            cudaStream_t st);
+
+constexpr int TC_K_ALIGN = 32;  // split-K ranges must be multiples of the 32-column TMA box
+
+}  // namespace gdr

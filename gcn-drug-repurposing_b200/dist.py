@@ -143,3 +143,239 @@ class RowPartitionedSpMM:
         self.csr_own.spmm(self.xbuf, out=self.y)                 # touches only the own rows of xbuf
         cur.wait_stream(self.comm_stream)
         return self.csr_rem.spmm(self.xbuf, e1=self.y, out=self.y)
+
+
+# ======================================================================================================
+# L-shaped partition: rows stay with their owner, but a block whose COLUMN owner has the higher rank is
+# multiplied there and its partial output rows are sent back ("push"), instead of pulling the X rows.
+# ======================================================================================================
+"""Why.  On skewed (R-MAT) graphs the row blocks of the low ranks are hub rows: rank 0's rows reference most
+columns of every other rank (pull volume ~ |unique columns| per block), while the block has few rows, so
+shipping the block's PARTIAL OUTPUT ROWS (|non-empty rows| per block) is several times cheaper.  With
+contiguous nnz-ordered blocks the cheaper direction is, to a good approximation, "block (r, s) is computed
+by rank max(r, s)":
+    r > s  (lower triangle)  pull:  rank s sends the referenced rows of X_s to r,      r computes Â[r,s]·X_s
+    r < s  (upper triangle)  push:  rank s computes Â[r,s]·X_s from its OWN X block,   sends the non-empty
+                                    output rows to r, which adds them in fixed rank order (deterministic).
+Rank s therefore owns an L-shaped region of Â (its row block left of the diagonal, plus its column block
+above the diagonal); bounds are chosen so that the L-shapes, not the row blocks, carry equal cost.  Measured
+on R-MAT scale 20, p = 8: bottleneck volume (max over ranks of rows sent or received) 496 K -> 323 K rows.
+
+The second gain is the dependency structure: the push product needs only the rank's own X, so it runs while
+the X rows travel; the partial rows travel while the pull product runs; only the final add waits.  No product
+is split into extra passes over Y."""
+
+
+def coarse_histogram(row_global, col_global, n, bins):
+    """[bins, bins] int64 counts of entries per (row bin, column bin); bin = index // ceil(n / bins)."""
+    size = -(-n // bins)
+    key = (row_global // size) * bins + (col_global // size)
+    return torch.bincount(key, minlength=bins * bins).reshape(bins, bins), size
+
+
+def lshape_bounds(hist, bin_size, n, parts, row_weight=6.0):
+    """Bounds [parts+1] (multiples of bin_size, last = n) that minimise the largest L-shape cost
+        cost(s) = nnz(L_s) + row_weight * (own rows + expected non-empty rows of the push blocks computed here
+                                           + add pass: own rows + expected partial rows received),
+    by bisection on the cost cap with a greedy left-to-right fill.  hist: numpy [B, B] from
+    coarse_histogram (summed over ranks)."""
+    hist = np.asarray(hist, dtype=np.float64)
+    nb = hist.shape[0]
+    sq = np.zeros(nb + 1)
+    sq[1:] = np.diagonal(hist.cumsum(0).cumsum(1))                      # nnz of the leading square [0,b)x[0,b)
+    ccum = np.zeros((nb, nb + 1))
+    ccum[:, 1:] = hist.cumsum(1)                                         # per row bin, cumulative over columns
+    rows_in = np.minimum(np.arange(1, nb + 1) * bin_size, n) - np.minimum(np.arange(nb) * bin_size, n)
+
+    def costs_from(b0):
+        """cost of an L-shape starting at bin b0 for every end bin b1 in (b0, nb]  -> array [nb - b0]."""
+        ends = np.arange(b0 + 1, nb + 1)
+        c = sq[ends] - sq[b0]
+        own = np.minimum(ends * bin_size, n) - min(b0 * bin_size, n)
+        if b0 > 0:
+            lam = (ccum[:b0, b0 + 1:nb + 1] - ccum[:b0, b0:b0 + 1]) / np.maximum(rows_in[:b0, None], 1)
+            push_rows = (rows_in[:b0, None] * (1.0 - np.exp(-lam))).sum(0)
+        else:
+            push_rows = 0.0
+        # add pass of this rank: partial rows arrive for its rows that have entries right of the block
+        right = ccum[b0:, nb:nb + 1] - ccum[b0:, b0 + 1:nb + 1]            # [row bin >= b0, end bin]: nnz in cols >= end
+        lam_r = right / np.maximum(rows_in[b0:, None], 1)
+        got = rows_in[b0:, None] * (1.0 - np.exp(-lam_r))                   # expected rows with a partial, per row bin
+        tri = np.tril(np.ones((nb - b0, nb - b0)), 0).T                     # row bin i (offset) counts for ends > i
+        recv_rows = (got * tri).sum(0)
+        add = np.where(recv_rows > 0, own + recv_rows, 0.0)
+        return np.maximum.accumulate(c + row_weight * (own + push_rows + add))
+
+    def fill(cap):
+        b, out = 0, [0]
+        for _ in range(parts):
+            if b >= nb:
+                out.append(nb)
+                continue
+            c = costs_from(b)
+            k = int(np.searchsorted(c, cap, side="right"))               # number of end bins with cost <= cap
+            b = b + max(k, 1)
+            out.append(min(b, nb))
+        return out
+
+    lo, hi = 0.0, float(costs_from(0)[-1])
+    for _ in range(40):
+        mid = 0.5 * (lo + hi)
+        if fill(mid)[-1] >= nb:
+            hi = mid
+        else:
+            lo = mid
+    b = fill(hi)
+    b[-1] = nb
+    return np.minimum(np.asarray(b, dtype=np.int64) * bin_size, n)
+
+
+def csr_from_sorted_rows(row, col, val, n_rows, n_cols):
+    """CSR from entries already ordered by (row, then the wanted in-row order).  Pure torch (CPU or CUDA)."""
+    rp = torch.zeros(n_rows + 1, dtype=torch.int64, device=row.device)
+    if row.numel():
+        rp[1:] = torch.cumsum(torch.bincount(row, minlength=n_rows), 0)
+    return DeviceCSR(rp.to(torch.int32), col.to(torch.int32).contiguous(), val.contiguous(), n_rows, n_cols)
+
+
+def _a2a_var(t, send_splits, group):
+    """Variable all-to-all of a 1-D tensor: exchanges the counts first; returns (received, recv_splits)."""
+    dev = t.device
+    s = torch.tensor(send_splits, dtype=torch.int64, device=dev)
+    r = torch.empty_like(s)
+    dist.all_to_all_single(r, s, group=group)
+    recv_splits = r.tolist()
+    out = torch.empty(int(sum(recv_splits)), dtype=t.dtype, device=dev)
+    dist.all_to_all_single(out, t.contiguous(), recv_splits, list(send_splits), group=group)
+    return out, recv_splits
+
+
+class LShapedSpMM:
+    """Rank s's share of Y = Â·X under the L-shaped partition (see the comment above).  Construct from the
+    rank's ROW block (global column ids); the entries above the diagonal are redistributed to their column
+    owners once, here.  Per-step buffers and index lists are fixed at construction.
+
+    Attributes the step uses (all on the local device):
+      xbuf = [x_own | x_recv]   own X rows, then the referenced rows of ranks 0..s-1 (owner order)
+      xsend, send_idx           rows of x_own packed for ranks s+1.., and their local ids
+      pull                      CSR  n_own x (n_own + n_xrecv): own row block, columns <= own block
+      push                      CSR  n_psend x n_own: blocks (a, s), a < s, non-empty rows only, stacked by a
+      psend / precv             partial output rows to ranks < s / from ranks > s
+      add                       CSR  n_own x n_precv of ones: which received partial rows add into which row
+    """
+
+    def __init__(self, local_csr, bounds, rank, world, d, group=None, comm_stream=None, group_partials=None):
+        """group_partials: a second communicator for the partial-row exchange, so that it can run while the
+        X-row exchange is still in flight (opposite directions on full-duplex links); default: `group`."""
+        self.bounds = [int(b) for b in bounds]
+        self.rank, self.world, self.d, self.group = rank, world, d, group
+        self.group_partials = group_partials if group_partials is not None else group
+        self.two_comms = group_partials is not None
+        dev = local_csr.device
+        s = rank
+        lo, hi = self.bounds[s], self.bounds[s + 1]
+        self.n, self.n_own = self.bounds[-1], hi - lo
+        bnd = torch.tensor(self.bounds, dtype=torch.int64, device=dev)
+        col = local_csr.col.to(torch.int64)
+        deg = (local_csr.rowptr[1:] - local_csr.rowptr[:-1]).to(torch.int64)
+        row = torch.repeat_interleave(torch.arange(self.n_own, device=dev), deg)
+        owner = torch.searchsorted(bnd, col, right=True) - 1
+        val = local_csr.val
+
+        # ---- pull part: columns owned by ranks <= s ----------------------------------------------------
+        keep = owner <= s
+        kcol, krow, kval = col[keep], row[keep], val[keep]
+        need_from, new_col, _ = plan_exchange(kcol, self.bounds, s)       # owners > s get empty lists
+        self.xrecv_splits = [int(t.numel()) for t in need_from]
+        n_xrecv = int(sum(self.xrecv_splits))
+        self.pull = csr_from_sorted_rows(krow, new_col, kval, self.n_own, self.n_own + n_xrecv)
+        want = torch.cat(need_from) if n_xrecv else torch.zeros(0, dtype=torch.int64, device=dev)
+        self.send_idx, self.xsend_splits = _a2a_var(want, self.xrecv_splits, group)
+
+        # ---- push part: entries above the diagonal go to their column owner, once ----------------------
+        up = ~keep
+        uo = owner[up]
+        order = torch.argsort(uo, stable=True)                            # by owner, row-major inside
+        cnt = torch.bincount(uo, minlength=world).tolist()
+        g_row, _ = _a2a_var((row[up] + lo)[order], cnt, group)
+        g_col, _ = _a2a_var(col[up][order], cnt, group)
+        g_val, from_counts = _a2a_var(val[up][order], cnt, group)         # arrives grouped by source rank
+        src = torch.repeat_interleave(torch.arange(world, device=dev),
+                                      torch.tensor(from_counts, dtype=torch.int64, device=dev))
+        # non-empty rows per source block, in (source, row) order = the layout of psend
+        rows_u, inv = torch.unique(g_row, return_inverse=True)            # sorted global rows => grouped by source
+        self.n_psend = int(rows_u.numel())
+        self.push = csr_from_sorted_rows(inv, g_col - lo, g_val, self.n_psend, self.n_own)
+        cut = torch.searchsorted(rows_u, bnd)
+        self.psend_splits = [int(cut[a + 1] - cut[a]) for a in range(world)]
+        back = rows_u - bnd[torch.searchsorted(bnd, rows_u, right=True) - 1]   # owner-local row ids
+        add_rows, self.precv_splits = _a2a_var(back, self.psend_splits, group)
+        self.n_precv = int(add_rows.numel())
+        pos = torch.arange(self.n_precv, device=dev)
+        o2 = torch.argsort(add_rows, stable=True)                         # by row; sources stay in rank order
+        self.add = csr_from_sorted_rows(add_rows[o2], pos[o2], torch.ones(self.n_precv, dtype=val.dtype, device=dev),
+                                        self.n_own, max(self.n_precv, 1))
+        del src
+
+        # ---- per-step buffers ---------------------------------------------------------------------------
+        f = dict(dtype=val.dtype, device=dev)
+        self.xbuf = torch.empty(self.n_own + n_xrecv, d, **f)
+        self.x_own, self.x_recv = self.xbuf[:self.n_own], self.xbuf[self.n_own:]
+        self.xsend = torch.empty(int(self.send_idx.numel()), d, **f)
+        self.psend = torch.empty(self.n_psend, d, **f)
+        self.precv = torch.empty(max(self.n_precv, 1), d, **f)[:self.n_precv]
+        self.y = torch.empty(self.n_own, d, **f)
+        self.recv_rows = n_xrecv + self.n_precv
+        self.sent_rows = int(self.send_idx.numel()) + self.n_psend
+        self.nnz_local = self.pull.nnz + self.push.nnz
+        self.comm_stream = comm_stream
+        if self.comm_stream is None and dev.type == "cuda":
+            self.comm_stream = torch.cuda.Stream(device=dev, priority=-1)
+        self.comm_stream2 = (torch.cuda.Stream(device=dev, priority=-1)
+                             if (self.two_comms and dev.type == "cuda") else self.comm_stream)
+        self.transport = "nccl all_to_all x2 (X rows to higher ranks, partial Y rows to lower ranks), L-shaped partition"
+
+    @classmethod
+    def from_full(cls, full_csr, bounds, rank, world, d, group=None, group_partials=None):
+        lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+        p0, p1 = int(full_csr.rowptr[lo].item()), int(full_csr.rowptr[hi].item())
+        local = DeviceCSR((full_csr.rowptr[lo:hi + 1] - p0).contiguous(), full_csr.col[p0:p1].clone(),
+                          full_csr.val[p0:p1].clone(), hi - lo, full_csr.n_cols)
+        return cls(local, bounds, rank, world, d, group, group_partials=group_partials)
+
+    # the two exchanges, separately callable (tests replace the device products around them)
+    def exchange_x(self):
+        if self.xsend.numel():
+            _ffi.check(_ffi.lib().gdr_gather_rows_f32(_ffi.ptr(self.x_own), _ffi.ptr(self.send_idx),
+                                                      self.send_idx.numel(), self.n_own, self.d,
+                                                      _ffi.ptr(self.xsend), _ffi.stream()), "gather_rows")
+        dist.all_to_all_single(self.x_recv, self.xsend, self.xrecv_splits, self.xsend_splits, group=self.group)
+
+    def exchange_partials(self):
+        dist.all_to_all_single(self.precv, self.psend, self.precv_splits, self.psend_splits,
+                               group=self.group_partials)
+
+    def spmm(self, x_local=None):
+        """Y_block = (Â·X)[lo:hi]; x_local = this rank's rows of X (None: already written into self.x_own)."""
+        if x_local is not None and x_local.data_ptr() != self.x_own.data_ptr():
+            self.x_own.copy_(x_local)
+        cur = torch.cuda.current_stream()
+        cs, cs2 = self.comm_stream, self.comm_stream2
+        cs.wait_stream(cur)
+        with torch.cuda.stream(cs):
+            self.exchange_x()
+            ev_x = cs.record_event()
+        if self.n_psend:
+            self.push.spmm(self.x_own, out=self.psend)                    # needs only the own X block
+        ev_p = cur.record_event()
+        with torch.cuda.stream(cs2):
+            cs2.wait_event(ev_p)
+            self.exchange_partials()
+            ev_y = cs2.record_event()
+        if self.x_recv.shape[0]:
+            cur.wait_event(ev_x)                                          # rank 0 pulls nothing: no wait
+        self.pull.spmm(self.xbuf, out=self.y)
+        cur.wait_event(ev_y)
+        if self.n_precv:
+            self.add.spmm(self.precv, e1=self.y, out=self.y)              # fixed (row, source rank) order
+        return self.y

@@ -12,6 +12,8 @@ the C ABI (include/gdr.h); autograd sees each forward as one custom Function who
 launches the kernels autograd would otherwise derive op by op.  CUDA tensors only: a CPU tensor
 raises (there is no CPU implementation on the product path).
 """
+import os
+
 import numpy as np
 import torch
 import torch.nn as nn
@@ -19,6 +21,12 @@ from torch.nn.parameter import Parameter
 
 from . import _ffi
 from .graph import device_csr_of
+
+# Which kernel family runs the dense contractions (X·Wᵀ, dZ·W, dZᵀ·P):
+#   "tc"   tcgen05 tensor cores, 3xTF32 split with fp32-level error (csrc/gemm_tc.cu)
+#   "simt" exact-fp32 FFMA tiles (csrc/gemm_simt.cuh)
+# Both are CUDA; this is a kernel choice, not a fallback.  Override with GDR_GEMM=simt|tc.
+GEMM_BACKEND = os.environ.get("GDR_GEMM", "simt")
 
 
 # --------------------------------------------------------------------------------------------
@@ -41,6 +49,13 @@ def layer_forward_raw(csr, x, w1, b1, w2, b2, residual, decay):
     t = csr.spmm(p, mul=x)               # model.py:168-169 (torch.mul folded into the gather)
     z = torch.empty_like(x)
     xnext = torch.empty_like(x)
+    if GEMM_BACKEND == "tc":
+        ws = _ffi.workspace(L.gdr_gcn_layer_fwd_tc_workspace_bytes(n, d), x.device)
+        _ffi.check(L.gdr_gcn_layer_fwd_tc_f32(_ffi.ptr(p), _ffi.ptr(t), _ffi.ptr(w1), _ffi.ptr(b1), _ffi.ptr(w2),
+                                              _ffi.ptr(b2), _ffi.ptr(residual), float(decay), n, d, _ffi.ptr(z),
+                                              _ffi.ptr(xnext), _ffi.ptr(ws), ws.numel(), _ffi.stream()),
+                   "gcn_layer_fwd_tc")
+        return p, t, z, xnext
     _ffi.check(L.gdr_gcn_layer_fwd_f32(_ffi.ptr(p), _ffi.ptr(t), _ffi.ptr(w1), _ffi.ptr(b1), _ffi.ptr(w2),
                                        _ffi.ptr(b2), _ffi.ptr(residual), float(decay), n, d, _ffi.ptr(z),
                                        _ffi.ptr(xnext), _ffi.stream()), "gcn_layer_fwd")
@@ -54,6 +69,24 @@ def layer_backward_raw(csr_t, gz, x, p, t, w1, w2, grads, accumulate, need_gx, w
     n, d = x.shape
     dw1, db1, dw2, db2 = grads
     acc = 1 if accumulate else 0
+    if GEMM_BACKEND == "tc":
+        wsw = _ffi.workspace(L.gdr_linear_bwd_weight_tc_workspace_bytes(n, d), x.device)
+        _ffi.check(L.gdr_linear_bwd_weight_tc_f32(_ffi.ptr(gz), _ffi.ptr(p), n, d, acc, _ffi.ptr(dw1), _ffi.ptr(db1),
+                                                  _ffi.ptr(wsw), wsw.numel(), _ffi.stream()), "linear_bwd_weight_tc(W1)")
+        _ffi.check(L.gdr_linear_bwd_weight_tc_f32(_ffi.ptr(gz), _ffi.ptr(t), n, d, acc, _ffi.ptr(dw2), _ffi.ptr(db2),
+                                                  _ffi.ptr(wsw), wsw.numel(), _ffi.stream()), "linear_bwd_weight_tc(W2)")
+        if not need_gx:
+            return None
+        wsi = _ffi.workspace(L.gdr_linear_bwd_input_tc_workspace_bytes(n, d), x.device)
+        gt = torch.empty_like(x)
+        _ffi.check(L.gdr_linear_bwd_input_tc_f32(_ffi.ptr(gz), _ffi.ptr(w2), None, None, n, d, _ffi.ptr(gt),
+                                                 _ffi.ptr(wsi), wsi.numel(), _ffi.stream()), "linear_bwd_input_tc(W2)")
+        gr = csr_t.spmm(gt)
+        gp = gt
+        _ffi.check(L.gdr_linear_bwd_input_tc_f32(_ffi.ptr(gz), _ffi.ptr(w1), _ffi.ptr(gr), _ffi.ptr(x), n, d,
+                                                 _ffi.ptr(gp), _ffi.ptr(wsi), wsi.numel(), _ffi.stream()),
+                   "linear_bwd_input_tc(W1)")
+        return csr_t.spmm(gp, e1=gr, e2=p)
     _ffi.check(L.gdr_linear_bwd_weight_f32(_ffi.ptr(gz), _ffi.ptr(p), n, d, acc, _ffi.ptr(dw1), _ffi.ptr(db1),
                                            _ffi.ptr(ws), ws.numel(), _ffi.stream()), "linear_bwd_weight(W1)")
     _ffi.check(L.gdr_linear_bwd_weight_f32(_ffi.ptr(gz), _ffi.ptr(t), n, d, acc, _ffi.ptr(dw2), _ffi.ptr(db2),

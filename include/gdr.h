@@ -32,6 +32,7 @@ extern "C" {
 #define GDR_E_BADARG (-1)   /* null pointer, negative size */
 #define GDR_E_SHAPE (-2)    /* unsupported width / alignment */
 #define GDR_E_WORKSPACE (-3) /* workspace too small */
+#define GDR_E_INTERNAL (-5) /* driver entry point missing / tensor-map encode failed */
 #define GDR_E_NOCONV (-4)   /* power iteration hit max_iter (reference raises, diffusion_profiles.py:90) */
 
 typedef void *gdr_stream_t; /* cudaStream_t */
@@ -143,6 +144,29 @@ int64_t gdr_linear_bwd_weight_workspace_bytes(int64_t n, int64_t d);
 int gdr_linear_bwd_weight_f32(const float *g, const float *a, int64_t n, int64_t d,
                               int accumulate, float *dw, float *db, void *workspace,
                               int64_t workspace_bytes, gdr_stream_t stream);
+
+/* ---- the same contractions on tcgen05 tensor cores (3xTF32: hi/lo TF32 split of both operands,
+ * three kind::tf32 MMAs per K step, corrections and K chunks in separate TMEM accumulators, summed in
+ * fp32 RN in the epilogue; TMA-fed, csrc/gemm_tc.cu).  Same arguments and results (to fp32 rounding
+ * noise) as the functions above, plus a caller-owned workspace for the split operands.               */
+int64_t gdr_gemm_nt_tc_workspace_bytes(int64_t m, int64_t n, int64_t k);
+/* C[m,n] = A[m,k]·B[n,k]ᵀ, row-major, K contiguous: torch.mm(A, B.T) / np.dot(H, H.T) (train.py:166) */
+int gdr_gemm_nt_tc_f32(const float *a, int64_t lda, const float *b, int64_t ldb, int64_t m, int64_t n,
+                       int64_t k, float *c, int64_t ldc, void *workspace, int64_t workspace_bytes,
+                       gdr_stream_t stream);
+int64_t gdr_gcn_layer_fwd_tc_workspace_bytes(int64_t n, int64_t d);
+int gdr_gcn_layer_fwd_tc_f32(const float *p, const float *t, const float *w1, const float *b1,
+                             const float *w2, const float *b2, const float *residual, float decay,
+                             int64_t n, int64_t d, float *z_out, float *xnext_out, void *workspace,
+                             int64_t workspace_bytes, gdr_stream_t stream);
+int64_t gdr_linear_bwd_input_tc_workspace_bytes(int64_t n, int64_t d);
+int gdr_linear_bwd_input_tc_f32(const float *g, const float *w, const float *e1, const float *e2,
+                                int64_t n, int64_t d, float *c_out, void *workspace,
+                                int64_t workspace_bytes, gdr_stream_t stream);
+int64_t gdr_linear_bwd_weight_tc_workspace_bytes(int64_t n, int64_t d);
+int gdr_linear_bwd_weight_tc_f32(const float *g, const float *a, int64_t n, int64_t d, int accumulate,
+                                 float *dw, float *db, void *workspace, int64_t workspace_bytes,
+                                 gdr_stream_t stream);
 
 /* ---- GSS loss ----------------------------------------------------------------------- *
  * GSS_loss.gss_loss (modules/model.py:214-221):  E = embs[index]; G = E·Eᵀ;

@@ -106,3 +106,102 @@ def test_plan_exchange_renumbering():
     assert own.tolist() == [False, True, False, True, False, True, False, False]
     # compact buffer: [own 4 rows | from rank 0: cols 0,1,3 | from rank 2: cols 8,9]
     assert new_col.tolist() == [4, 1, 8, 1, 6, 3, 7, 5]
+
+
+# ---- L-shaped partition (push blocks above the diagonal) -------------------------------------------------
+def _skewed_matrix(n, seed):
+    """Rows and columns both skewed towards low indices (R-MAT-like), plus the identity."""
+    rng = np.random.default_rng(seed)
+    m = 40 * n
+    r = np.minimum((rng.random(m) ** 3 * n).astype(np.int64), n - 1)
+    c = np.minimum((rng.random(m) ** 3 * n).astype(np.int64), n - 1)
+    a = sp.coo_matrix((rng.random(m).astype(np.float32) + 0.1, (r, c)), shape=(n, n)).tocsr()
+    a = (a + sp.identity(n, dtype=np.float32)).tocsr().astype(np.float32)
+    a.sort_indices()
+    return a
+
+
+def _lshape_worker(rank, world, port, n, d, out):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    import gdr_b200  # noqa: F401
+    from gdr_b200 import dist as gdist
+    from gdr_b200.graph import DeviceCSR
+    m = _skewed_matrix(n, 5)
+    x = np.random.default_rng(6).standard_normal((n, d)).astype(np.float32)
+    coo = m.tocoo()
+    hist, size = gdist.coarse_histogram(torch.from_numpy(coo.row.astype(np.int64)),
+                                        torch.from_numpy(coo.col.astype(np.int64)), n, 64)
+    bounds = gdist.lshape_bounds(hist.numpy(), size, n, world, row_weight=2.0)
+    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+    blk = m[lo:hi]
+    local = DeviceCSR(torch.from_numpy(blk.indptr.astype(np.int32)), torch.from_numpy(blk.indices.astype(np.int32)),
+                      torch.from_numpy(blk.data), hi - lo, n)
+    part = gdist.LShapedSpMM(local, bounds, rank, world, d)
+
+    def to_sp(c):
+        return sp.csr_matrix((c.val.numpy(), c.col.numpy(), c.rowptr.numpy()), shape=(c.n_rows, c.n_cols))
+
+    # one step with the device kernels replaced by torch/scipy equivalents, same order as LShapedSpMM.spmm
+    part.x_own.copy_(torch.from_numpy(x[lo:hi]))
+    part.xsend.copy_(part.x_own[part.send_idx])                                    # = gdr_gather_rows_f32
+    dist.all_to_all_single(part.x_recv, part.xsend, part.xrecv_splits, part.xsend_splits)
+    if part.n_psend:
+        part.psend.copy_(torch.from_numpy(to_sp(part.push) @ part.x_own.numpy()))
+    part.exchange_partials()
+    y = to_sp(part.pull) @ part.xbuf.numpy()
+    if part.n_precv:
+        y = y + to_sp(part.add)[:, :part.n_precv] @ part.precv.numpy()
+    exp = blk @ x
+    ok = np.allclose(y, exp, rtol=1e-5, atol=1e-5)
+    # bookkeeping: every entry of the matrix is multiplied exactly once, somewhere
+    nnz_all = torch.tensor([part.pull.nnz + part.push.nnz], dtype=torch.int64)
+    dist.all_reduce(nnz_all)
+    # the pull part never references columns of higher ranks; the push part only own columns
+    own_cols_only = part.push.nnz == 0 or int(part.push.col.max()) < part.n_own
+    no_recv_from_higher = all(c == 0 for c in part.xrecv_splits[rank:])
+    no_partials_from_lower = all(c == 0 for c in part.precv_splits[:rank + 1])
+    out.put((rank, bool(ok), int(nnz_all.item()) == m.nnz, bool(own_cols_only and no_recv_from_higher
+                                                                  and no_partials_from_lower),
+             part.recv_rows, part.pull.nnz + part.push.nnz, [int(b) for b in bounds]))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_lshaped_partition_gloo(world):
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    n = 700
+    procs = [ctx.Process(target=_lshape_worker, args=(r, world, port, n, 8, out)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [out.get(timeout=180) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(r[1] for r in res), res                    # product equals the row block of the full product
+    assert all(r[2] for r in res), res                    # no entry lost or duplicated
+    assert all(r[3] for r in res), res                    # direction of both exchanges
+    bounds = res[0][6]
+    assert bounds[0] == 0 and bounds[-1] == n and all(b1 >= b0 for b0, b1 in zip(bounds, bounds[1:]))
+    loads = [r[5] for r in sorted(res)]
+    assert max(loads) < 1.5 * sum(loads) / world, loads  # L-shapes, not row blocks, carry equal nnz
+
+
+def test_lshape_bounds_balances_l_shapes():
+    import gdr_b200  # noqa: F401
+    from gdr_b200 import dist as gdist
+    m = _skewed_matrix(4000, 2).tocoo()
+    hist, size = gdist.coarse_histogram(torch.from_numpy(m.row.astype(np.int64)),
+                                        torch.from_numpy(m.col.astype(np.int64)), 4000, 128)
+    assert int(hist.sum()) == m.nnz
+    b = gdist.lshape_bounds(hist.numpy(), size, 4000, 4, row_weight=0.0)
+    assert b[0] == 0 and b[-1] == 4000 and (np.diff(b) > 0).all()
+    blk_r = np.searchsorted(b, m.row, side="right") - 1
+    blk_c = np.searchsorted(b, m.col, side="right") - 1
+    load = np.bincount(np.maximum(blk_r, blk_c), minlength=4)      # block (r, s) is computed by max(r, s)
+    assert load.sum() == m.nnz and load.max() < 1.25 * m.nnz / 4, load
+    assert gdist.lshape_bounds(hist.numpy(), size, 4000, 1).tolist() == [0, 4000]
