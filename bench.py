@@ -52,6 +52,9 @@ def parse_args():
     p.add_argument("--no-rmat", action="store_true", help="skip the secondary R-MAT SpMM measurement at N=1")
     p.add_argument("--no-cpu-baseline", action="store_true")
     p.add_argument("--no-overlap", action="store_true", help="N>1: exchange first, then one local SpMM")
+    p.add_argument("--transport", choices=["p2p", "nccl"], default="p2p",
+                   help="N>1, lshape: direct stores into peer symmetric memory, or NCCL all_to_all of packed rows")
+    p.add_argument("--push-ctas", type=int, default=0, help="CTAs of the p2p push kernel (0: library default)")
     p.add_argument("--two-comms", action="store_true", help="N>1, lshape: partial rows on a second NCCL communicator")
     p.add_argument("--partition", choices=["lshape", "rows"], default="lshape",
                    help="N>1: L-shaped partition (blocks above the diagonal are multiplied at the column owner and "
@@ -424,7 +427,8 @@ def run_rmat_spmm_dist(args):
     if args.partition == "lshape":
         g2 = dist.new_group(backend="nccl", pg_options=dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)) \
             if args.two_comms else None
-        part = gdist.LShapedSpMM.from_full(full, bounds, rank, world, d, group_partials=g2)
+        part = gdist.LShapedSpMM.from_full(full, bounds, rank, world, d, group_partials=g2,
+                                           transport=args.transport, push_ctas=args.push_ctas)
     else:
         part = gdist.RowPartitionedSpMM.from_full(full, bounds, rank, world, d, overlap=not args.no_overlap)
     del full

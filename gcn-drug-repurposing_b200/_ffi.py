@@ -57,11 +57,19 @@ _SIGNATURES = {
     "gdr_linear_bwd_input_tc_f32": (c_i32, [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_i64, c_ptr]),
     "gdr_linear_bwd_weight_tc_workspace_bytes": (c_i64, [c_i64, c_i64]),
     "gdr_linear_bwd_weight_tc_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i64, c_i32, c_ptr, c_ptr, c_ptr, c_i64, c_ptr]),
+    "gdr_gss_loss_tc_workspace_bytes": (c_i64, [c_i64, c_i64]),
+    "gdr_gss_loss_fwd_bwd_tc_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_f32, c_f32, c_ptr, c_ptr, c_ptr,
+                                            c_i64, c_ptr]),
+    "gdr_gram_percentile_tc_workspace_bytes": (c_i64, [c_i64, c_i64]),
+    "gdr_gram_percentile_tc_f32": (c_i32, [c_ptr, c_i64, c_i64, c_f64, ctypes.POINTER(c_f32), c_ptr, c_i64, c_ptr]),
     "gdr_gather_rows_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr]),
     "gdr_scatter_rows_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr]),
     "gdr_gram_percentile_workspace_bytes": (c_i64, [c_i64, c_i64]),
     "gdr_gram_percentile_f32": (c_i32, [c_ptr, c_i64, c_i64, c_f64, ctypes.POINTER(c_f32), c_ptr, c_i64, c_ptr]),
     "gdr_gram_topk_f64": (c_i32, [c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr]),
+    "gdr_push_rows_f32": (c_i32, [c_ptr, c_i64, c_i32, c_ptr, c_ptr, c_ptr, c_ptr, c_i32, c_ptr]),
+    "gdr_adam_step_multi_f32": (c_i32, [c_i32, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_f64, c_f64, c_f64, c_f64,
+                                        c_ptr]),
     "gdr_adam_step_f32": (c_i32, [c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_f32, c_f32, c_f32, c_f32, c_ptr, c_ptr]),
     "gdr_rwr_workspace_bytes": (c_i64, [c_i64, c_i64, c_i64]),
     "gdr_rwr_solve_f64": (c_i32, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_i64,

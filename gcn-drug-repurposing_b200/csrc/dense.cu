@@ -95,16 +95,31 @@ splitk_reduce_kernel(const float *__restrict__ part, int splits, int64_t count, 
   out[i] = accumulate ? out[i] + s : s;
 }
 
-// column sums of G[n,d] -> partial[blocks][d]; each block owns a row slab
-constexpr int CS_ROWS = 256;
+// column sums of G[n,d] -> partial[blocks][d]; each block owns a slab of CS_ROWS rows.  256 threads =
+// 64 float4 column groups x 4 row lanes (4 rows in flight per column group), fixed-order combine in
+// shared memory: deterministic.
+constexpr int CS_ROWS = 128;
 __global__ void __launch_bounds__(256)
 colsum_partial_kernel(const float *__restrict__ g, int64_t n, int64_t d, float *__restrict__ part) {
+  __shared__ float4 red[4][64];
   const int64_t r0 = (int64_t)blockIdx.x * CS_ROWS;
   const int64_t r1 = min(n, r0 + CS_ROWS);
-  for (int64_t c = threadIdx.x; c < d; c += blockDim.x) {
-    float s = 0.f;
-    for (int64_t r = r0; r < r1; ++r) s += g[r * d + c];
-    part[(int64_t)blockIdx.x * d + c] = s;
+  const int cg = threadIdx.x & 63, rl = threadIdx.x >> 6;
+  for (int64_t c = (int64_t)cg * 4; c < d; c += 256) {  // d % 4 == 0
+    float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int64_t r = r0 + rl; r < r1; r += 4) {
+      const float4 v = ldg_f4(g + r * d + c);
+      s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+    }
+    red[rl][cg] = s;
+    __syncthreads();
+    if (rl == 0) {
+      const float4 a = red[0][cg], b = red[1][cg], e = red[2][cg], f = red[3][cg];
+      *reinterpret_cast<float4 *>(part + (int64_t)blockIdx.x * d + c) =
+          make_float4((a.x + b.x) + (e.x + f.x), (a.y + b.y) + (e.y + f.y), (a.z + b.z) + (e.z + f.z),
+                      (a.w + b.w) + (e.w + f.w));
+    }
+    __syncthreads();
   }
 }
 

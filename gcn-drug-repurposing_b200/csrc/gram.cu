@@ -5,7 +5,7 @@
 //                            train.py:165-167
 #include <math.h>
 
-#include "gemm_simt.cuh"
+#include "gemm_tc.cuh"
 
 namespace gdr {
 
@@ -198,18 +198,31 @@ int64_t gdr_gram_percentile_workspace_bytes(int64_t n, int64_t d) {
   return align_up(GHIST_BINS * 8, 256) + 1024;
 }
 
-int gdr_gram_percentile_f32(const float *h, int64_t n, int64_t d, double q_percent, float *beta_out_host,
-                            void *workspace, int64_t workspace_bytes, gdr_stream_t stream) {
+int64_t gdr_gram_percentile_tc_workspace_bytes(int64_t n, int64_t d) {
+  if (n <= 0 || d <= 0) return GDR_E_BADARG;
+  return align_up(GHIST_BINS * 8, 256) + 1024 + 2 * align_up(n * d * 4, 256);
+}
+
+static int gram_percentile_impl(const float *h, int64_t n, int64_t d, double q_percent, float *beta_out_host,
+                                void *workspace, int64_t workspace_bytes, gdr_stream_t stream, bool use_tc) {
   GDR_CHECK_ARG(n > 0 && d > 0 && h && beta_out_host && workspace, GDR_E_BADARG, "gram_percentile: bad args");
   GDR_CHECK_ARG(d % 4 == 0, GDR_E_SHAPE, "gram_percentile: d must be a multiple of 4");
   GDR_CHECK_ARG(q_percent >= 0.0 && q_percent <= 100.0, GDR_E_BADARG, "gram_percentile: q outside [0,100]");
-  GDR_CHECK_ARG(workspace_bytes >= gdr_gram_percentile_workspace_bytes(n, d), GDR_E_WORKSPACE,
-                "gram_percentile: workspace too small");
+  GDR_CHECK_ARG(workspace_bytes >= (use_tc ? gdr_gram_percentile_tc_workspace_bytes(n, d)
+                                           : gdr_gram_percentile_workspace_bytes(n, d)),
+                GDR_E_WORKSPACE, "gram_percentile: workspace too small");
   GDR_CHECK_ARG((double)n * (double)n < 9.0e15, GDR_E_SHAPE, "gram_percentile: n*n exceeds the exact fp64 index range");
   cudaStream_t st = as_stream(stream);
   Carver cv(workspace);
   unsigned long long *hist = cv.take<unsigned long long>(GHIST_BINS);
   SelectState *sel = cv.take<SelectState>(1);
+  float *hhi = nullptr, *hlo = nullptr;
+  if (use_tc) {
+    hhi = cv.take<float>(n * d);
+    hlo = cv.take<float>(n * d);
+    const int rc = tc_split(h, d, d, nullptr, 0, 0, n, hhi, hlo, st);
+    if (rc) return rc;
+  }
 
   // numpy's virtual index for method='linear' (alpha = beta = 1), same expression and rounding:
   //   n*q + (alpha + q*(1 - alpha - beta)) - 1          numpy/lib/_function_base_impl.py
@@ -235,8 +248,13 @@ int gdr_gram_percentile_f32(const float *h, int64_t n, int64_t d, double q_perce
   for (int pass = 0; pass < 3; ++pass) {
     g.shift = shifts[pass];
     g.bin_mask = (unsigned int)(bins[pass] - 1);
-    gemm_f32_kernel<true, true, EPI_HIST><<<grid, GTHREADS, 0, st>>>(g);
-    GDR_LAUNCHED();
+    if (use_tc) {
+      const int rc = tc_gemm(EPI_HIST, hhi, hlo, hhi, hlo, n, n, d, d, d, d, 1, g, st);
+      if (rc) return rc;
+    } else {
+      gemm_f32_kernel<true, true, EPI_HIST><<<grid, GTHREADS, 0, st>>>(g);
+      GDR_LAUNCHED();
+    }
     select_descend_kernel<<<1, 256, 0, st>>>(sel, hist, shifts[pass], bins[pass]);
     GDR_LAUNCHED();
   }
@@ -246,8 +264,13 @@ int gdr_gram_percentile_f32(const float *h, int64_t n, int64_t d, double q_perce
   const float v_lo = f32_from_key(hs.prefix);
   float v_hi = v_lo;
   if (gamma > 0.0 && hs.rank + 1 >= hs.count) {  // the next order statistic is a larger value
-    gemm_f32_kernel<true, true, EPI_MINGT><<<grid, GTHREADS, 0, st>>>(g);
-    GDR_LAUNCHED();
+    if (use_tc) {
+      const int rc = tc_gemm(EPI_MINGT, hhi, hlo, hhi, hlo, n, n, d, d, d, d, 1, g, st);
+      if (rc) return rc;
+    } else {
+      gemm_f32_kernel<true, true, EPI_MINGT><<<grid, GTHREADS, 0, st>>>(g);
+      GDR_LAUNCHED();
+    }
     GDR_CUDA(cudaMemcpyAsync(&hs, sel, sizeof(SelectState), cudaMemcpyDeviceToHost, st));
     GDR_CUDA(cudaStreamSynchronize(st));
     if (hs.min_gt != 0xffffffffu) v_hi = f32_from_key(hs.min_gt);
@@ -259,6 +282,17 @@ int gdr_gram_percentile_f32(const float *h, int64_t n, int64_t d, double q_perce
   if (gamma >= 0.5) r = (double)v_hi - (double)diff * (1.0 - gamma);
   *beta_out_host = (float)r;
   return GDR_OK;
+}
+
+int gdr_gram_percentile_f32(const float *h, int64_t n, int64_t d, double q_percent, float *beta_out_host,
+                            void *workspace, int64_t workspace_bytes, gdr_stream_t stream) {
+  return gram_percentile_impl(h, n, d, q_percent, beta_out_host, workspace, workspace_bytes, stream, false);
+}
+
+// the same order statistic with the recomputed Gram tiles on the tensor cores (3xTF32, gemm_tc.cu)
+int gdr_gram_percentile_tc_f32(const float *h, int64_t n, int64_t d, double q_percent, float *beta_out_host,
+                               void *workspace, int64_t workspace_bytes, gdr_stream_t stream) {
+  return gram_percentile_impl(h, n, d, q_percent, beta_out_host, workspace, workspace_bytes, stream, true);
 }
 
 }  // extern "C"

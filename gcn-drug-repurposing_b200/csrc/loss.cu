@@ -6,7 +6,7 @@
 //
 // Forward and gradient come out of one call: the Gram GEMM's epilogue turns each G tile
 // into (loss partial, 2·dG tile) in registers, a second GEMM contracts 2·dG with E.
-#include "gemm_simt.cuh"
+#include "gemm_tc.cuh"
 
 namespace gdr {
 
@@ -77,6 +77,34 @@ adam_kernel(float *__restrict__ p, const float *__restrict__ g, float *__restric
 }
 
 __global__ void bump_step_kernel(int32_t *step_dev) { *step_dev += 1; }
+
+// all parameter tensors of the model in ONE launch (train.py:139 builds Adam over 4 tensors)
+constexpr int ADAM_MAX_TENSORS = 16;
+struct AdamMulti {
+  float *p[ADAM_MAX_TENSORS];
+  const float *g[ADAM_MAX_TENSORS];
+  float *m[ADAM_MAX_TENSORS];
+  float *v[ADAM_MAX_TENSORS];
+  int64_t end[ADAM_MAX_TENSORS];  // exclusive prefix ends of the concatenated index space
+  int n;
+};
+__global__ void __launch_bounds__(256)
+adam_multi_kernel(const AdamMulti a, int64_t total, float step_size, float bc2_sqrt, float omb1, float b2, float omb2,
+                  float eps) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= total) return;
+  int t = 0;
+  while (i >= a.end[t]) ++t;
+  const int64_t j = i - (t ? a.end[t - 1] : 0);
+  const float gi = a.g[t][j];
+  float mi = a.m[t][j], vi = a.v[t][j];
+  mi = mi + (gi - mi) * omb1;                              // exp_avg.lerp_(grad, 1 - beta1)
+  vi = __fadd_rn(__fmul_rn(vi, b2), omb2 * gi * gi);       // exp_avg_sq.mul_(beta2).addcmul_(grad, grad, 1 - beta2)
+  a.m[t][j] = mi;
+  a.v[t][j] = vi;
+  const float denom = sqrtf(vi) / bc2_sqrt + eps;
+  a.p[t][j] = a.p[t][j] - step_size * (mi / denom);
+}
 
 }  // namespace gdr
 
@@ -164,6 +192,80 @@ int gdr_adam_step_f32(float *param, const float *grad, float *exp_avg, float *ex
                                                                       beta1, beta2, eps, step_dev);
   GDR_LAUNCHED();
   bump_step_kernel<<<1, 1, 0, st>>>(step_dev);
+  GDR_LAUNCHED();
+  return GDR_OK;
+}
+
+// ---- tcgen05 variant: Gram and dG·E on the tensor cores (3xTF32, csrc/gemm_tc.cu) -------------------------
+int64_t gdr_gss_loss_tc_workspace_bytes(int64_t b, int64_t d) {
+  if (b < 0 || d <= 0) return GDR_E_BADARG;
+  const int64_t ldw = align_up(b, 4);
+  const int64_t tiles = ceil_div<int64_t>(b > 0 ? b : 1, 128);
+  return 3 * align_up(b * d * 4, 256) + 3 * align_up(b * ldw * 4, 256) + 2 * align_up(d * ldw * 4, 256) +
+         align_up(tiles * tiles * 8, 256) + 2048;
+}
+
+int gdr_gss_loss_fwd_bwd_tc_f32(const float *embs, const int64_t *index, int64_t b, int64_t n, int64_t d, float alpha,
+                                float beta, float *loss_out, float *grad_e_out, void *workspace,
+                                int64_t workspace_bytes, gdr_stream_t stream) {
+  GDR_CHECK_ARG(b > 0 && n > 0 && d > 0, GDR_E_BADARG, "gss_loss_tc: bad sizes");
+  GDR_CHECK_ARG(d % 4 == 0, GDR_E_SHAPE, "gss_loss_tc: d must be a multiple of 4");
+  GDR_CHECK_ARG(embs && loss_out && grad_e_out && workspace, GDR_E_BADARG, "gss_loss_tc: null pointer");
+  GDR_CHECK_ARG(workspace_bytes >= gdr_gss_loss_tc_workspace_bytes(b, d), GDR_E_WORKSPACE,
+                "gss_loss_tc: workspace too small (B=%lld needs BxB tile buffers)", (long long)b);
+  cudaStream_t st = as_stream(stream);
+  const int64_t ldw = align_up(b, 4);
+  const int64_t tiles = ceil_div<int64_t>(b, 128);
+  Carver cv(workspace);
+  float *e = cv.take<float>(b * d), *ehi = cv.take<float>(b * d), *elo = cv.take<float>(b * d);
+  float *wm = cv.take<float>(b * ldw), *whi = cv.take<float>(b * ldw), *wlo = cv.take<float>(b * ldw);
+  float *ethi = cv.take<float>(d * ldw), *etlo = cv.take<float>(d * ldw);
+  double *partials = cv.take<double>(tiles * tiles);
+  gather_rows_kernel<<<(unsigned)ceil_div<int64_t>(b * 32, 256), 256, 0, st>>>(embs, index, b, n, d, e);
+  GDR_LAUNCHED();
+  int rc;
+  if ((rc = tc_split(e, d, d, nullptr, 0, 0, b, ehi, elo, st))) return rc;
+  if ((rc = tc_split_transpose(e, d, b, d, ldw, ethi, etlo, st))) return rc;  // Eᵀ [d, ldw], zero padded
+  GemmParams g{};
+  g.c = wm; g.ldc = ldw;
+  g.alpha = alpha; g.beta = beta;
+  g.wscale = (float)(2.0 / ((double)b * (double)b));
+  g.loss_partials = partials;
+  if ((rc = tc_gemm(EPI_GSS, ehi, elo, ehi, elo, b, b, d, d, d, d, 1, g, st))) return rc;   // G = E·Eᵀ -> loss, 2·dG
+  loss_finalize_kernel<<<1, 256, 0, st>>>(partials, (int)(tiles * tiles), 1.0 / ((double)b * (double)b), loss_out);
+  GDR_LAUNCHED();
+  if ((rc = tc_split(wm, ldw, ldw, nullptr, 0, 0, b, whi, wlo, st))) return rc;
+  GemmParams q{};
+  q.c = grad_e_out; q.ldc = d;
+  return tc_gemm(EPI_STORE, whi, wlo, ethi, etlo, b, d, ldw, ldw, ldw, ldw, 1, q, st);       // dE = 2·dG · E
+}
+
+int gdr_adam_step_multi_f32(int n_tensors, float *const *params, const float *const *grads, float *const *exp_avg,
+                            float *const *exp_avg_sq, const int64_t *counts, int64_t step, double lr, double beta1,
+                            double beta2, double eps, gdr_stream_t stream) {
+  GDR_CHECK_ARG(n_tensors >= 0 && n_tensors <= ADAM_MAX_TENSORS, GDR_E_SHAPE, "adam_step_multi: at most %d tensors",
+                ADAM_MAX_TENSORS);
+  GDR_CHECK_ARG(step >= 1, GDR_E_BADARG, "adam_step_multi: step counts from 1");
+  if (n_tensors == 0) return GDR_OK;
+  GDR_CHECK_ARG(params && grads && exp_avg && exp_avg_sq && counts, GDR_E_BADARG, "adam_step_multi: null table");
+  AdamMulti a{};
+  int64_t total = 0;
+  for (int t = 0; t < n_tensors; ++t) {
+    GDR_CHECK_ARG(params[t] && grads[t] && exp_avg[t] && exp_avg_sq[t] && counts[t] >= 0, GDR_E_BADARG,
+                  "adam_step_multi: tensor %d", t);
+    a.p[t] = params[t]; a.g[t] = grads[t]; a.m[t] = exp_avg[t]; a.v[t] = exp_avg_sq[t];
+    total += counts[t];
+    a.end[t] = total;
+  }
+  a.n = n_tensors;
+  if (total == 0) return GDR_OK;
+  // torch/optim/adam.py (_single_tensor_adam): every scalar (1 - beta, bias corrections, step size) is a python
+  // double, rounded to fp32 only when it meets the tensor
+  const double bc1 = 1.0 - pow(beta1, (double)step);
+  const double bc2 = 1.0 - pow(beta2, (double)step);
+  adam_multi_kernel<<<(unsigned)ceil_div<int64_t>(total, 256), 256, 0, as_stream(stream)>>>(
+      a, total, (float)(lr / bc1), (float)sqrt(bc2), (float)(1.0 - beta1), (float)beta2, (float)(1.0 - beta2),
+      (float)eps);
   GDR_LAUNCHED();
   return GDR_OK;
 }

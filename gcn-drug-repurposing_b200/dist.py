@@ -264,9 +264,12 @@ class LShapedSpMM:
       add                       CSR  n_own x n_precv of ones: which received partial rows add into which row
     """
 
-    def __init__(self, local_csr, bounds, rank, world, d, group=None, comm_stream=None, group_partials=None):
+    def __init__(self, local_csr, bounds, rank, world, d, group=None, comm_stream=None, group_partials=None,
+                 transport="nccl", push_ctas=0):
         """group_partials: a second communicator for the partial-row exchange, so that it can run while the
-        X-row exchange is still in flight (opposite directions on full-duplex links); default: `group`."""
+        X-row exchange is still in flight (opposite directions on full-duplex links); default: `group`.
+        transport: "nccl" (all_to_all of packed rows) or "p2p" (gdr_push_rows_f32: rows are stored straight into
+        the destination's receive region over NVLink; buffers live in symmetric memory)."""
         self.bounds = [int(b) for b in bounds]
         self.rank, self.world, self.d, self.group = rank, world, d, group
         self.group_partials = group_partials if group_partials is not None else group
@@ -319,11 +322,16 @@ class LShapedSpMM:
 
         # ---- per-step buffers ---------------------------------------------------------------------------
         f = dict(dtype=val.dtype, device=dev)
-        self.xbuf = torch.empty(self.n_own + n_xrecv, d, **f)
+        self.p2p = transport == "p2p"
+        self.push_ctas = int(push_ctas)
+        if self.p2p:
+            self._setup_p2p(n_xrecv, f)
+        else:
+            self.xbuf = torch.empty(self.n_own + n_xrecv, d, **f)
+            self.precv = torch.empty(max(self.n_precv, 1), d, **f)[:self.n_precv]
+            self.xsend = torch.empty(int(self.send_idx.numel()), d, **f)
         self.x_own, self.x_recv = self.xbuf[:self.n_own], self.xbuf[self.n_own:]
-        self.xsend = torch.empty(int(self.send_idx.numel()), d, **f)
         self.psend = torch.empty(self.n_psend, d, **f)
-        self.precv = torch.empty(max(self.n_precv, 1), d, **f)[:self.n_precv]
         self.y = torch.empty(self.n_own, d, **f)
         self.recv_rows = n_xrecv + self.n_precv
         self.sent_rows = int(self.send_idx.numel()) + self.n_psend
@@ -332,19 +340,72 @@ class LShapedSpMM:
         if self.comm_stream is None and dev.type == "cuda":
             self.comm_stream = torch.cuda.Stream(device=dev, priority=-1)
         self.comm_stream2 = (torch.cuda.Stream(device=dev, priority=-1)
-                             if (self.two_comms and dev.type == "cuda") else self.comm_stream)
-        self.transport = "nccl all_to_all x2 (X rows to higher ranks, partial Y rows to lower ranks), L-shaped partition"
+                             if ((self.two_comms or self.p2p) and dev.type == "cuda") else self.comm_stream)
+        self.transport = ("p2p stores into peer symmetric memory (gdr_push_rows_f32) x2" if self.p2p else
+                          "nccl all_to_all x2") + " (X rows to higher ranks, partial Y rows to lower ranks), L-shaped partition"
+
+    def _setup_p2p(self, n_xrecv, f):
+        """xbuf and precv of every rank in ONE symmetric allocation; destination addresses of both pushes."""
+        import ctypes
+        import torch.distributed._symmetric_memory as symm
+        s, world, d = self.rank, self.world, self.d
+        meta = [None] * world
+        dist.all_gather_object(meta, dict(n_own=self.n_own, xrecv=self.xrecv_splits, precv=self.precv_splits),
+                               group=self.group)
+        xrows_max = max(m["n_own"] + sum(m["xrecv"]) for m in meta)
+        prows_max = max(max(sum(m["precv"]) for m in meta), 1)
+        self._symm_t = symm.empty((xrows_max + prows_max) * d, dtype=f["dtype"], device=f["device"])
+        gname = (self.group or dist.group.WORLD).group_name
+        self._hdl = symm.rendezvous(self._symm_t, gname)
+        buf = self._symm_t.view(xrows_max + prows_max, d)
+        self.xbuf = buf[:self.n_own + n_xrecv]
+        self.precv = buf[xrows_max:xrows_max + self.n_precv]
+        self.xsend = torch.empty(0, d, **f)                                  # no pack buffer on this transport
+        esz = self._symm_t.element_size()
+        base = [int(p) for p in self._hdl.buffer_ptrs]
+        arr, i64 = ctypes.c_void_p * world, ctypes.c_int64 * world
+        # X rows: to every r > s, into r's xbuf after r's own rows and the rows of ranks < s
+        xdst, xidx, xcnt, off = [None] * world, [None] * world, [0] * world, 0
+        for r in range(world):
+            c = self.xsend_splits[r]
+            if c:
+                xdst[r] = base[r] + (meta[r]["n_own"] + sum(meta[r]["xrecv"][:s])) * d * esz
+                xidx[r] = self.send_idx.data_ptr() + off * 8
+                xcnt[r] = c
+            off += c
+        self._xpush = (arr(*xdst), arr(*xidx), i64(*([0] * world)), i64(*xcnt))
+        # partial rows: to every a < s, contiguous slices of psend, into a's precv after the rows of ranks < s
+        pdst, pcnt, poff, off = [None] * world, [0] * world, [0] * world, 0
+        for a in range(world):
+            c = self.psend_splits[a]
+            if c:
+                pdst[a] = base[a] + (xrows_max + sum(meta[a]["precv"][:s])) * d * esz
+                poff[a], pcnt[a] = off, c
+            off += c
+        self._ppush = (arr(*pdst), arr(*([None] * world)), i64(*poff), i64(*pcnt))
+
+    def _push(self, src, table):
+        dst, idx, off, cnt = table
+        _ffi.check(_ffi.lib().gdr_push_rows_f32(_ffi.ptr(src) if src.numel() else None, self.d, self.world, dst, idx,
+                                                off, cnt, self.push_ctas, _ffi.stream()), "push_rows")
 
     @classmethod
-    def from_full(cls, full_csr, bounds, rank, world, d, group=None, group_partials=None):
+    def from_full(cls, full_csr, bounds, rank, world, d, group=None, group_partials=None, **kw):
         lo, hi = int(bounds[rank]), int(bounds[rank + 1])
         p0, p1 = int(full_csr.rowptr[lo].item()), int(full_csr.rowptr[hi].item())
         local = DeviceCSR((full_csr.rowptr[lo:hi + 1] - p0).contiguous(), full_csr.col[p0:p1].clone(),
                           full_csr.val[p0:p1].clone(), hi - lo, full_csr.n_cols)
-        return cls(local, bounds, rank, world, d, group, group_partials=group_partials)
+        return cls(local, bounds, rank, world, d, group, group_partials=group_partials, **kw)
 
     # the two exchanges, separately callable (tests replace the device products around them)
     def exchange_x(self):
+        if self.p2p:
+            self._hdl.barrier(channel=0)            # every rank is done reading last step's xbuf / precv
+            self._ev_b0 = torch.cuda.current_stream().record_event()
+            if self.send_idx.numel():
+                self._push(self.x_own, self._xpush)
+            self._hdl.barrier(channel=1)            # every rank's rows have landed
+            return
         if self.xsend.numel():
             _ffi.check(_ffi.lib().gdr_gather_rows_f32(_ffi.ptr(self.x_own), _ffi.ptr(self.send_idx),
                                                       self.send_idx.numel(), self.n_own, self.d,
@@ -352,6 +413,12 @@ class LShapedSpMM:
         dist.all_to_all_single(self.x_recv, self.xsend, self.xrecv_splits, self.xsend_splits, group=self.group)
 
     def exchange_partials(self):
+        if self.p2p:
+            torch.cuda.current_stream().wait_event(self._ev_b0)
+            if self.n_psend:
+                self._push(self.psend, self._ppush)
+            self._hdl.barrier(channel=2)
+            return
         dist.all_to_all_single(self.precv, self.psend, self.precv_splits, self.psend_splits,
                                group=self.group_partials)
 

@@ -47,10 +47,16 @@ def gram_percentile(h, q):
         raise RuntimeError("gram_percentile: expected an fp32 CUDA tensor (no CPU implementation)")
     h = h.contiguous()
     n, d = h.shape
-    ws = _ffi.workspace(L.gdr_gram_percentile_workspace_bytes(n, d), h.device)
     out = ctypes.c_float(0.0)
-    _ffi.check(L.gdr_gram_percentile_f32(_ffi.ptr(h), n, d, float(q), ctypes.byref(out), _ffi.ptr(ws), ws.numel(),
-                                         _ffi.stream()), "gram_percentile_f32")
+    from . import model as _model
+    if _model.GEMM_BACKEND == "tc":
+        ws = _ffi.workspace(L.gdr_gram_percentile_tc_workspace_bytes(n, d), h.device)
+        _ffi.check(L.gdr_gram_percentile_tc_f32(_ffi.ptr(h), n, d, float(q), ctypes.byref(out), _ffi.ptr(ws),
+                                                ws.numel(), _ffi.stream()), "gram_percentile_tc_f32")
+    else:
+        ws = _ffi.workspace(L.gdr_gram_percentile_workspace_bytes(n, d), h.device)
+        _ffi.check(L.gdr_gram_percentile_f32(_ffi.ptr(h), n, d, float(q), ctypes.byref(out), _ffi.ptr(ws), ws.numel(),
+                                             _ffi.stream()), "gram_percentile_f32")
     return np.float32(out.value)
 
 

@@ -26,7 +26,7 @@ from .graph import device_csr_of
 #   "tc"   tcgen05 tensor cores, 3xTF32 split with fp32-level error (csrc/gemm_tc.cu)
 #   "simt" exact-fp32 FFMA tiles (csrc/gemm_simt.cuh)
 # Both are CUDA; this is a kernel choice, not a fallback.  Override with GDR_GEMM=simt|tc.
-GEMM_BACKEND = os.environ.get("GDR_GEMM", "simt")
+GEMM_BACKEND = os.environ.get("GDR_GEMM", "tc")
 
 
 # --------------------------------------------------------------------------------------------
@@ -225,10 +225,16 @@ class _GSSLossFunction(torch.autograd.Function):
             b = n
         loss = torch.empty((), dtype=torch.float32, device=e.device)
         ge = torch.empty(b, d, dtype=torch.float32, device=e.device)
-        ws = _ffi.workspace(L.gdr_gss_loss_workspace_bytes(b, d), e.device)
-        _ffi.check(L.gdr_gss_loss_fwd_bwd_f32(_ffi.ptr(e), _ffi.ptr(index), b, n, d, float(alpha), float(beta),
-                                              _ffi.ptr(loss), _ffi.ptr(ge), _ffi.ptr(ws), ws.numel(),
-                                              _ffi.stream()), "gss_loss_fwd_bwd")
+        if GEMM_BACKEND == "tc":
+            ws = _ffi.workspace(L.gdr_gss_loss_tc_workspace_bytes(b, d), e.device)
+            _ffi.check(L.gdr_gss_loss_fwd_bwd_tc_f32(_ffi.ptr(e), _ffi.ptr(index), b, n, d, float(alpha), float(beta),
+                                                     _ffi.ptr(loss), _ffi.ptr(ge), _ffi.ptr(ws), ws.numel(),
+                                                     _ffi.stream()), "gss_loss_fwd_bwd_tc")
+        else:
+            ws = _ffi.workspace(L.gdr_gss_loss_workspace_bytes(b, d), e.device)
+            _ffi.check(L.gdr_gss_loss_fwd_bwd_f32(_ffi.ptr(e), _ffi.ptr(index), b, n, d, float(alpha), float(beta),
+                                                  _ffi.ptr(loss), _ffi.ptr(ge), _ffi.ptr(ws), ws.numel(),
+                                                  _ffi.stream()), "gss_loss_fwd_bwd")
         ctx.index = index
         ctx.shape = (n, d)
         ctx.save_for_backward(ge)

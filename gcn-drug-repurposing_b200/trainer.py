@@ -15,6 +15,7 @@ import numpy as np
 import torch
 
 from .dataset import DiffusionDataLoader, DiffusionDataSet
+from .optim import Adam
 from .helper import (combine_graph, convert_sparse_matrix_to_sparse_tensor, gen_graph, gram_percentile,
                      preprocess_graph)
 from .model import GSS_loss, ResidualGraphConvolutionalNetwork
@@ -67,7 +68,7 @@ class GCNTrainer:
                                                        init_weights=init_weights, layer_decay=layer_decay)
         self.model.to(self.device)
         self.model.train()
-        self.optimizer = torch.optim.Adam(self.model.parameters(), lr=lr, weight_decay=0)
+        self.optimizer = Adam(self.model.parameters(), lr=lr, weight_decay=0)       # train.py:139-141
         self.loss_fcn = GSS_loss(alpha).gss_loss
         self.beta = beta
         self.beta_percentile = beta_percentile

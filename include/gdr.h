@@ -168,6 +168,15 @@ int gdr_linear_bwd_weight_tc_f32(const float *g, const float *a, int64_t n, int6
                                  float *dw, float *db, void *workspace, int64_t workspace_bytes,
                                  gdr_stream_t stream);
 
+int64_t gdr_gss_loss_tc_workspace_bytes(int64_t b, int64_t d);
+int gdr_gss_loss_fwd_bwd_tc_f32(const float *embs, const int64_t *index, int64_t b, int64_t n, int64_t d,
+                                float alpha, float beta, float *loss_out, float *grad_e_out,
+                                void *workspace, int64_t workspace_bytes, gdr_stream_t stream);
+int64_t gdr_gram_percentile_tc_workspace_bytes(int64_t n, int64_t d);
+int gdr_gram_percentile_tc_f32(const float *h, int64_t n, int64_t d, double q_percent,
+                               float *beta_out_host, void *workspace, int64_t workspace_bytes,
+                               gdr_stream_t stream);
+
 /* ---- GSS loss ----------------------------------------------------------------------- *
  * GSS_loss.gss_loss (modules/model.py:214-221):  E = embs[index]; G = E·Eᵀ;
  * loss = mean(-0.5*alpha*(relu(G)-beta)^2).  One call gives the loss and dLoss/dE
@@ -180,6 +189,12 @@ int gdr_gss_loss_fwd_bwd_f32(const float *embs, const int64_t *index, int64_t b,
 /* dst[i,:] = src[index[i],:]  (embs[index], model.py:216; also the send-buffer pack of the partitioned SpMM) */
 int gdr_gather_rows_f32(const float *src, const int64_t *index, int64_t b, int64_t n, int64_t d,
                         float *dst, gdr_stream_t stream);
+/* The exchange step of the partitioned SpMM as direct stores into peer memory (NVLink P2P): for every
+ * destination k, dst[k][j,:] = src[idx[k][j],:] (idx[k] == NULL: rows src_off[k]+j).  dst[k] may be a peer-GPU
+ * address obtained from a symmetric-memory rendezvous.  Tables are HOST arrays (n_dst <= 16).  Replaces
+ * gdr_gather_rows_f32 + ncclSend of the packed buffer.  n_ctas <= 0: default.                            */
+int gdr_push_rows_f32(const float *src, int64_t d, int n_dst, float *const *dst, const int64_t *const *idx,
+                      const int64_t *src_off, const int64_t *counts, int n_ctas, gdr_stream_t stream);
 /* gh[index[i],:] += scale_dev[0] * ge[i,:]  (autograd of embs[index]); gh pre-zeroed. */
 int gdr_scatter_rows_f32(const float *ge, const int64_t *index, int64_t b, int64_t n,
                          int64_t d, const float *scale_dev, float *gh, gdr_stream_t stream);
@@ -206,6 +221,12 @@ int gdr_gram_topk_f64(const double *x, int64_t n, int64_t d, int64_t k,
 int gdr_adam_step_f32(float *param, const float *grad, float *exp_avg, float *exp_avg_sq,
                       int64_t count, float lr, float beta1, float beta2, float eps,
                       int32_t *step_dev, gdr_stream_t stream);
+/* The same update for up to 16 parameter tensors in one launch (train.py:139 hands Adam four).  The tables
+ * are HOST arrays of device pointers / element counts; `step` is the 1-based step number of this update.   */
+int gdr_adam_step_multi_f32(int n_tensors, float *const *params, const float *const *grads,
+                            float *const *exp_avg, float *const *exp_avg_sq, const int64_t *counts,
+                            int64_t step, double lr, double beta1, double beta2, double eps,
+                            gdr_stream_t stream);
 
 /* ---- diffusion profiles (multiscale/diff_prof/diffusion_profiles.py:29-90) ----------- *
  * Batched personalised-PageRank power iteration for `n_seeds` seeds at once, each with the

@@ -65,8 +65,14 @@ def test_layer_forward_tc_matches_simt(gdr):
                                                       ws.numel(), gdr._ffi.stream()))
         torch.cuda.synchronize()
         out[name] = (z.cpu().numpy(), y.cpu().numpy())
-    assert_close(out["tc"][0], out["simt"][0], what="Z tc vs simt")
-    assert_close(out["tc"][1], out["simt"][1], what="Xnext tc vs simt")
+    # generic operands (|P·W| sums ~500 terms of mixed sign): two fp32 implementations differ by a few 1e-6 here, so
+    # the yardstick is fp64 and the budget is the exact-fp32 kernel's own error
+    z64 = (p.double() @ w1.double().T + b1.double() + t.double() @ w2.double().T + b2.double()).cpu().numpy()
+    y64 = res.double().cpu().numpy() + 0.3 * np.where(z64 > 0, z64, np.expm1(z64))
+    for i, (nm, ref) in enumerate((("Z", z64), ("Xnext", y64))):
+        e_tc, e_simt = np.abs(out["tc"][i] - ref).max(), np.abs(out["simt"][i] - ref).max()
+        print(f"\n[layer fwd {nm}] max abs err vs fp64: tc {e_tc:.3e} simt {e_simt:.3e}")
+        assert e_tc <= max(2.0 * e_simt, 2e-6), f"{nm}: tc error {e_tc:.3e} vs exact-fp32 kernel {e_simt:.3e}"
 
 
 def test_linear_backward_tc_matches_simt(gdr):
@@ -98,7 +104,10 @@ def test_linear_backward_tc_matches_simt(gdr):
         torch.cuda.synchronize()
         res[name] = (c.cpu().numpy(), dw.cpu().numpy(), db.cpu().numpy())
     ref_dw = 1.0 + (gz.double().T @ a.double()).cpu().numpy()
-    assert_close(res["tc"][0], res["simt"][0], what="dX tc vs simt")
+    ref_dx = (gz.double() @ w.double() + e1.double() * e2.double()).cpu().numpy()
+    e_tc, e_simt = np.abs(res["tc"][0] - ref_dx).max(), np.abs(res["simt"][0] - ref_dx).max()
+    print(f"\n[dX] max abs err vs fp64: tc {e_tc:.3e} simt {e_simt:.3e}")
+    assert e_tc <= max(2.0 * e_simt, 2e-6)
     assert_close(res["tc"][2], res["simt"][2], what="db tc vs simt")
     # dW sums 3k products per entry: compare both against fp64, the tc error must be of the same order
     e_tc, e_simt = np.abs(res["tc"][1] - ref_dw).max(), np.abs(res["simt"][1] - ref_dw).max()
@@ -115,3 +124,70 @@ def test_training_steps_match_golden_with_tc_backend(gdr, monkeypatch):
         test_gpu_gcn.test_training_steps_match_reference(gdr, case)
     test_gpu_gcn.test_layer_forward_matches_reference(gdr)
     test_gpu_gcn.test_input_gradient_and_oracle_autograd(gdr)
+
+
+def test_gss_loss_tc_matches_simt(gdr, monkeypatch):
+    n, d, b = 1500, 128, 777                               # b not a multiple of 4: padded B x B buffers
+    g = torch.Generator(device=DEV).manual_seed(3)
+    h = torch.nn.functional.normalize(torch.randn(n, d, device=DEV, generator=g), dim=1)
+    idx = torch.randperm(n, device=DEV, generator=g)[:b]
+    out = {}
+    for name in ("simt", "tc"):
+        monkeypatch.setattr(gdr.model, "GEMM_BACKEND", name)
+        e = h.clone().requires_grad_(True)
+        loss = gdr.GSS_loss(1.0).gss_loss(embs=e, beta=0.2, index=idx)
+        loss.backward()
+        torch.cuda.synchronize()
+        out[name] = (loss.item(), e.grad.cpu().numpy())
+    assert_close(out["tc"][0], out["simt"][0], what="loss tc vs simt")
+    assert_close(out["tc"][1], out["simt"][1], what="dLoss/dE tc vs simt")
+    # and against torch autograd on the CPU (the reference's arithmetic, modules/model.py:214-221)
+    e = h.cpu().clone().requires_grad_(True)
+    ee = e[idx.cpu()]
+    gm = torch.mm(ee, ee.t())
+    ref = torch.mean(-0.5 * (torch.relu(gm) - 0.2) ** 2)
+    ref.backward()
+    assert_close(out["tc"][0], ref.item(), what="loss tc vs torch cpu")
+    assert_close(out["tc"][1], e.grad.numpy(), what="dLoss/dE tc vs torch cpu")
+
+
+@pytest.mark.parametrize("n,d,q", [(257, 128, 98.0), (600, 128, 98.0), (300, 256, 50.0), (130, 12, 0.0), (130, 12, 100.0)])
+def test_gram_percentile_tc(gdr, monkeypatch, n, d, q):
+    from . import test_gpu_gcn
+    monkeypatch.setattr(gdr.model, "GEMM_BACKEND", "tc")
+    test_gpu_gcn.test_gram_percentile_vs_numpy(gdr, n, d, q)
+
+
+def test_beta_selection_tc(gdr, monkeypatch):
+    from . import test_gpu_gcn
+    monkeypatch.setattr(gdr.model, "GEMM_BACKEND", "tc")
+    for case in ("gcn_knn257.npz", "gcn_knn600_l3.npz", "gcn_edge300_d256.npz"):
+        test_gpu_gcn.test_beta_selection_matches_reference(gdr, case)
+
+
+def test_fused_adam_matches_torch_adam(gdr):
+    """gdr.optim.Adam (one launch for all tensors) against torch.optim.Adam on the same gradients, 6 steps;
+    state_dict layouts are interchangeable."""
+    g = torch.Generator(device=DEV).manual_seed(5)
+    shapes = [(256, 256), (256,), (256, 256), (256,)]
+    p_ref = [torch.randn(*s, device=DEV, generator=g).requires_grad_(True) for s in shapes]
+    p_our = [p.detach().clone().requires_grad_(True) for p in p_ref]
+    o_ref = torch.optim.Adam(p_ref, lr=3e-4, weight_decay=0)
+    o_our = gdr.optim.Adam(p_our, lr=3e-4, weight_decay=0)
+    for step in range(6):
+        for a, b in zip(p_ref, p_our):
+            gr = torch.randn(a.shape, device=DEV, generator=g) * (10.0 ** (step - 3))
+            a.grad, b.grad = gr.clone(), gr.clone()
+        o_ref.step()
+        o_our.step()
+    torch.cuda.synchronize()
+    for a, b in zip(p_ref, p_our):
+        assert_close(b.detach().cpu().numpy(), a.detach().cpu().numpy(), rtol=1e-6, atol=1e-7, what="param")
+    sd_ref, sd_our = o_ref.state_dict(), o_our.state_dict()
+    assert sd_ref["state"].keys() == sd_our["state"].keys()
+    for k in sd_ref["state"]:
+        assert set(sd_ref["state"][k]) == set(sd_our["state"][k]) == {"step", "exp_avg", "exp_avg_sq"}
+        assert float(sd_ref["state"][k]["step"]) == float(sd_our["state"][k]["step"]) == 6.0
+        assert_close(sd_our["state"][k]["exp_avg_sq"].cpu().numpy(), sd_ref["state"][k]["exp_avg_sq"].cpu().numpy(),
+                     rtol=1e-6, atol=0, what="exp_avg_sq")
+    o_ref.load_state_dict(sd_our)                          # the reference optimizer accepts our state
