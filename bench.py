@@ -55,6 +55,11 @@ def parse_args():
     p.add_argument("--transport", choices=["p2p", "nccl"], default="p2p",
                    help="N>1, lshape: direct stores into peer symmetric memory, or NCCL all_to_all of packed rows")
     p.add_argument("--push-ctas", type=int, default=0, help="CTAs of the p2p push kernel (0: library default)")
+    p.add_argument("--hubs", type=int, default=0,
+                   help="N>1, lshape: the lowest K ranks exchange through NVSwitch multicast (multimem broadcast of "
+                        "their X block, in-switch reduction of their partial rows)")
+    p.add_argument("--comm-weight", type=float, default=0.0,
+                   help="N>1, lshape: cost of one row moved, in nnz-equivalents, in the partition's balance")
     p.add_argument("--two-comms", action="store_true", help="N>1, lshape: partial rows on a second NCCL communicator")
     p.add_argument("--partition", choices=["lshape", "rows"], default="lshape",
                    help="N>1: L-shaped partition (blocks above the diagonal are multiplied at the column owner and "
@@ -406,7 +411,8 @@ def run_rmat_spmm_dist(args):
         row_of = torch.repeat_interleave(torch.arange(n, device=dev), deg)
         hist, bin_size = gdist.coarse_histogram(row_of, full.col.to(torch.int64), n, min(1024, n))
         del row_of, deg
-        bounds = gdist.lshape_bounds(hist.cpu().numpy(), bin_size, n, world, row_weight=args.row_weight)
+        bounds = gdist.lshape_bounds(hist.cpu().numpy(), bin_size, n, world, row_weight=args.row_weight,
+                                     comm_weight=args.comm_weight)
     else:
         rp = full.rowptr.cpu().numpy().astype(np.int64)
         bounds = gdist.nnz_balanced_bounds(rp + (np.arange(len(rp)) * args.row_weight).astype(np.int64), world)
@@ -427,8 +433,12 @@ def run_rmat_spmm_dist(args):
     if args.partition == "lshape":
         g2 = dist.new_group(backend="nccl", pg_options=dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)) \
             if args.two_comms else None
-        part = gdist.LShapedSpMM.from_full(full, bounds, rank, world, d, group_partials=g2,
-                                           transport=args.transport, push_ctas=args.push_ctas)
+        if args.hubs > 0:
+            part = gdist.NvlsLShapedSpMM.from_full(full, bounds, rank, world, d, n_hubs=args.hubs,
+                                                   push_ctas=args.push_ctas)
+        else:
+            part = gdist.LShapedSpMM.from_full(full, bounds, rank, world, d, group_partials=g2,
+                                               transport=args.transport, push_ctas=args.push_ctas)
     else:
         part = gdist.RowPartitionedSpMM.from_full(full, bounds, rank, world, d, overlap=not args.no_overlap)
     del full
@@ -459,16 +469,18 @@ def run_rmat_spmm_dist(args):
         if args.partition == "lshape":
             t_x = timed(part.exchange_x)
             nop = lambda: None                     # every rank must enter timed() (it holds a barrier)
-            t_push = timed((lambda: part.push.spmm(part.x_own, out=part.psend)) if part.n_psend else nop)
+            t_push = timed(part.push_product)
             t_p = timed(part.exchange_partials)
             t_pull = timed(lambda: part.pull.spmm(part.xbuf, out=part.y))
             t_add = timed((lambda: part.add.spmm(part.precv, e1=part.y, out=part.y)) if part.n_precv else nop)
+            t_red = timed(part.hub_reduce)
             t_all = timed(lambda: part.spmm(None))
             sys.stderr.write("[diag] rank %d rows %d | x-exchange %.2f ms (recv %d send %d rows) | push %.2f ms (nnz %d, "
                              "%d rows) | partial-exchange %.2f ms (recv %d) | pull %.2f ms (nnz %d) | add %.2f ms | "
-                             "step %.2f ms\n" % (rank, hi - lo, t_x, sum(part.xrecv_splits), int(part.send_idx.numel()),
-                                                 t_push, part.push.nnz, part.n_psend, t_p, part.n_precv, t_pull,
-                                                 part.pull.nnz, t_add, t_all))
+                             "hub-reduce %.2f ms | step %.2f ms\n" % (
+                                 rank, hi - lo, t_x, sum(part.xrecv_splits), int(part.send_idx.numel()), t_push,
+                                 part.push.nnz, part.n_psend, t_p, part.n_precv, t_pull, part.pull.nnz, t_add, t_red,
+                                 t_all))
             sys.stderr.flush()
         t_ex = 0.0 if args.partition == "lshape" else timed(part._exchange)
         if args.partition == "lshape":

@@ -36,6 +36,8 @@ _SIGNATURES = {
     "gdr_spmm_csr_f32": (c_i32, [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr]),
     "gdr_spmm_csr_planned_f32": (c_i32, [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i32,
                                          c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr]),
+    "gdr_spmm_csr_dual_f32": (c_i32, [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i32,
+                                      c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr]),
     "gdr_spmm_csr_f64": (c_i32, [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr]),
     "gdr_gcn_layer_fwd_f32": (c_i32, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_f32, c_i64, c_i64,
                                       c_ptr, c_ptr, c_ptr]),
@@ -67,6 +69,8 @@ _SIGNATURES = {
     "gdr_gram_percentile_workspace_bytes": (c_i64, [c_i64, c_i64]),
     "gdr_gram_percentile_f32": (c_i32, [c_ptr, c_i64, c_i64, c_f64, ctypes.POINTER(c_f32), c_ptr, c_i64, c_ptr]),
     "gdr_gram_topk_f64": (c_i32, [c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr]),
+    "gdr_mc_broadcast_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i32, c_ptr]),
+    "gdr_mc_reduce_add_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i32, c_ptr]),
     "gdr_push_rows_f32": (c_i32, [c_ptr, c_i64, c_i32, c_ptr, c_ptr, c_ptr, c_ptr, c_i32, c_ptr]),
     "gdr_adam_step_multi_f32": (c_i32, [c_i32, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_f64, c_f64, c_f64, c_f64,
                                         c_ptr]),

@@ -84,15 +84,24 @@ elu_bwd_kernel(const float *__restrict__ gxn, const float *__restrict__ z, const
   *reinterpret_cast<float4 *>(gz + i * 4) = o;
 }
 
-// split-K partial reduce: out[i] (+)= sum_z part[z][i], fixed order (deterministic)
+// split-K partial reduce: out[i] (+)= sum_z part[z][i].  A block owns 32 consecutive outputs; its 8 warps
+// stride over z (8 partial rows in flight, 128-byte coalesced each) and are combined in a fixed order in
+// shared memory, so the result is deterministic.
 __global__ void __launch_bounds__(256)
 splitk_reduce_kernel(const float *__restrict__ part, int splits, int64_t count, int accumulate,
                      float *__restrict__ out) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-  if (i >= count) return;
+  __shared__ float red[8][32];
+  const int o = threadIdx.x & 31, zl = threadIdx.x >> 5;
+  const int64_t i = (int64_t)blockIdx.x * 32 + o;
   float s = 0.f;
-  for (int z = 0; z < splits; ++z) s += part[(int64_t)z * count + i];
-  out[i] = accumulate ? out[i] + s : s;
+  if (i < count)
+    for (int z = zl; z < splits; z += 8) s += part[(int64_t)z * count + i];
+  red[zl][o] = s;
+  __syncthreads();
+  if (zl == 0 && i < count) {
+    const float t = ((red[0][o] + red[1][o]) + (red[2][o] + red[3][o])) + ((red[4][o] + red[5][o]) + (red[6][o] + red[7][o]));
+    out[i] = accumulate ? out[i] + t : t;
+  }
 }
 
 // column sums of G[n,d] -> partial[blocks][d]; each block owns a slab of CS_ROWS rows.  256 threads =
@@ -242,12 +251,12 @@ int gdr_linear_bwd_weight_f32(const float *g, const float *a, int64_t n, int64_t
   dim3 grid((unsigned)ceil_div<int64_t>(d, GBN), (unsigned)ceil_div<int64_t>(d, GBM), (unsigned)splits);
   gemm_f32_kernel<false, false, EPI_SPLITK><<<grid, GTHREADS, 0, st>>>(q);
   GDR_LAUNCHED();
-  splitk_reduce_kernel<<<(unsigned)ceil_div<int64_t>(d * d, 256), 256, 0, st>>>(part, splits, d * d, accumulate, dw);
+  splitk_reduce_kernel<<<(unsigned)ceil_div<int64_t>(d * d, 32), 256, 0, st>>>(part, splits, d * d, accumulate, dw);
   GDR_LAUNCHED();
   if (db) {
     colsum_partial_kernel<<<(unsigned)cs_blocks, 256, 0, st>>>(g, n, d, cpart);
     GDR_LAUNCHED();
-    splitk_reduce_kernel<<<(unsigned)ceil_div<int64_t>(d, 256), 256, 0, st>>>(cpart, (int)cs_blocks, d, accumulate,
+    splitk_reduce_kernel<<<(unsigned)ceil_div<int64_t>(d, 32), 256, 0, st>>>(cpart, (int)cs_blocks, d, accumulate,
                                                                              db);
     GDR_LAUNCHED();
   }
@@ -357,12 +366,12 @@ int gdr_linear_bwd_weight_tc_f32(const float *g, const float *a, int64_t n, int6
   GemmParams q{};
   q.c = part; q.ldc = d;
   if ((rc = tc_gemm(EPI_SPLITK, ghi, glo, ahi, alo, d, d, n, ldt, ldt, per, splits, q, st))) return rc;
-  splitk_reduce_kernel<<<(unsigned)ceil_div<int64_t>(d * d, 256), 256, 0, st>>>(part, splits, d * d, accumulate, dw);
+  splitk_reduce_kernel<<<(unsigned)ceil_div<int64_t>(d * d, 32), 256, 0, st>>>(part, splits, d * d, accumulate, dw);
   GDR_LAUNCHED();
   if (db) {
     colsum_partial_kernel<<<(unsigned)cs_blocks, 256, 0, st>>>(g, n, d, cpart);
     GDR_LAUNCHED();
-    splitk_reduce_kernel<<<(unsigned)ceil_div<int64_t>(d, 256), 256, 0, st>>>(cpart, (int)cs_blocks, d, accumulate,
+    splitk_reduce_kernel<<<(unsigned)ceil_div<int64_t>(d, 32), 256, 0, st>>>(cpart, (int)cs_blocks, d, accumulate,
                                                                              db);
     GDR_LAUNCHED();
   }

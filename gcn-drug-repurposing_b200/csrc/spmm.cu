@@ -136,6 +136,11 @@ struct SpmmPlan {
   const int4 *hub_info;
   int32_t *tickets;  // [n_hubs], zero on entry and on exit
   void *partial;     // [n_chunks, d]
+  // optional second output of the same launch: y2 = y ⊙ m2 (row-aligned with y).  The layer needs both
+  // P = Â·X and P ⊙ X (modules/model.py:163,168); writing the product here turns the next SpMM into a plain
+  // one-operand gather (half the gather traffic of multiplying inside the gather).
+  const void *m2;
+  void *y2;
 };
 
 // Row width d == 32 * VecOf<T>::N * V exactly (V slabs per lane).
@@ -198,6 +203,10 @@ spmm_warp_row_kernel(const int32_t *__restrict__ rowptr, const int32_t *__restri
       vadd(acc[v], a);
     }
     *reinterpret_cast<Vec *>(yr + v * SLAB) = acc[v];
+    if (plan.y2 != nullptr) {
+      const Vec m = vload<T>(static_cast<const T *>(plan.m2) + row * D + loff + v * SLAB);
+      *reinterpret_cast<Vec *>(static_cast<T *>(plan.y2) + row * D + loff + v * SLAB) = vmul(acc[v], m);
+    }
   }
 }
 
@@ -208,7 +217,7 @@ __global__ void __launch_bounds__(256)
 spmm_warp_row_generic_kernel(const int32_t *__restrict__ rowptr, const int32_t *__restrict__ col,
                              const T *__restrict__ val, int64_t n_rows, int64_t d, const T *__restrict__ x,
                              const T *__restrict__ mul, const T *__restrict__ e1, const T *__restrict__ e2,
-                             T *__restrict__ y) {
+                             T *__restrict__ y, const T *__restrict__ m2, T *__restrict__ y2) {
   using Vec = typename VecOf<T>::type;
   constexpr int EPL = VecOf<T>::N;
   constexpr int SLAB = 32 * EPL;
@@ -247,6 +256,7 @@ spmm_warp_row_generic_kernel(const int32_t *__restrict__ rowptr, const int32_t *
         vadd(acc, a);
       }
       *reinterpret_cast<Vec *>(y + row * d + cc) = acc;
+      if (y2 != nullptr) *reinterpret_cast<Vec *>(y2 + row * d + cc) = vmul(acc, vload<T>(m2 + row * d + cc));
     }
   }
 }
@@ -269,8 +279,9 @@ static int launch_spmm(const int32_t *rowptr, const int32_t *col, const T *val, 
   else if (d == 4 * SLAB)
     spmm_warp_row_kernel<T, 4, MUL, ADD><<<grid, T_, 0, st>>>(rowptr, col, val, n_rows, x, mul, e1, e2, y, plan);
   else
-    spmm_warp_row_generic_kernel<T, MUL, ADD><<<grid, T_, 0, st>>>(rowptr, col, val, n_rows, d, x, mul, e1, e2,
-                                                                  y);
+    spmm_warp_row_generic_kernel<T, MUL, ADD><<<grid, T_, 0, st>>>(rowptr, col, val, n_rows, d, x, mul, e1, e2, y,
+                                                                  static_cast<const T *>(plan.m2),
+                                                                  static_cast<T *>(plan.y2));
   GDR_LAUNCHED();
   return GDR_OK;
 }
@@ -287,11 +298,13 @@ using namespace gdr;
 
 extern "C" {
 
-int gdr_spmm_csr_planned_f32(const int32_t *rowptr, const int32_t *col, const float *val, int64_t n_rows,
-                             int64_t d, const float *x, const float *mul, const float *e1, const float *e2,
-                             float *y, int32_t hub_threshold, int64_t n_hubs, const int32_t *hub_info,
-                             int64_t n_chunks, const int32_t *chunk_info, int32_t *tickets, float *partial,
-                             gdr_stream_t stream) {
+static int spmm_f32_impl(const int32_t *rowptr, const int32_t *col, const float *val, int64_t n_rows, int64_t d,
+                         const float *x, const float *mul, const float *e1, const float *e2, float *y,
+                         const float *m2, float *y2, int32_t hub_threshold, int64_t n_hubs, const int32_t *hub_info,
+                         int64_t n_chunks, const int32_t *chunk_info, int32_t *tickets, float *partial,
+                         gdr_stream_t stream) {
+  GDR_CHECK_ARG((m2 == nullptr) == (y2 == nullptr), GDR_E_BADARG, "spmm_f32: m2 and y2 come together");
+  GDR_CHECK_ARG((((uintptr_t)m2 | (uintptr_t)y2) & 15) == 0, GDR_E_SHAPE, "spmm_f32: pointers must be 16-byte aligned");
   GDR_CHECK_ARG(n_rows >= 0 && d > 0, GDR_E_BADARG, "spmm_f32: bad sizes");
   GDR_CHECK_ARG(d % 4 == 0, GDR_E_SHAPE, "spmm_f32: d=%lld must be a multiple of 4", (long long)d);
   GDR_CHECK_ARG(rowptr && x && y, GDR_E_BADARG, "spmm_f32: null pointer");
@@ -313,10 +326,31 @@ int gdr_spmm_csr_planned_f32(const int32_t *rowptr, const int32_t *col, const fl
     plan.tickets = tickets;
     plan.partial = partial;
   }
+  plan.m2 = m2;
+  plan.y2 = y2;
   if (mul && e1) return launch_spmm<float, true, true>(rowptr, col, val, n_rows, d, x, mul, e1, e2, y, plan, st);
   if (mul) return launch_spmm<float, true, false>(rowptr, col, val, n_rows, d, x, mul, e1, e2, y, plan, st);
   if (e1) return launch_spmm<float, false, true>(rowptr, col, val, n_rows, d, x, mul, e1, e2, y, plan, st);
   return launch_spmm<float, false, false>(rowptr, col, val, n_rows, d, x, mul, e1, e2, y, plan, st);
+}
+
+int gdr_spmm_csr_planned_f32(const int32_t *rowptr, const int32_t *col, const float *val, int64_t n_rows,
+                             int64_t d, const float *x, const float *mul, const float *e1, const float *e2,
+                             float *y, int32_t hub_threshold, int64_t n_hubs, const int32_t *hub_info,
+                             int64_t n_chunks, const int32_t *chunk_info, int32_t *tickets, float *partial,
+                             gdr_stream_t stream) {
+  return spmm_f32_impl(rowptr, col, val, n_rows, d, x, mul, e1, e2, y, nullptr, nullptr, hub_threshold, n_hubs,
+                       hub_info, n_chunks, chunk_info, tickets, partial, stream);
+}
+
+// y = Â·x (+ e1 ⊙ e2) and, in the same launch, y2 = y ⊙ m2.  Plan arguments as above (n_chunks = 0: no plan).
+int gdr_spmm_csr_dual_f32(const int32_t *rowptr, const int32_t *col, const float *val, int64_t n_rows, int64_t d,
+                          const float *x, const float *e1, const float *e2, float *y, const float *m2, float *y2,
+                          int32_t hub_threshold, int64_t n_hubs, const int32_t *hub_info, int64_t n_chunks,
+                          const int32_t *chunk_info, int32_t *tickets, float *partial, gdr_stream_t stream) {
+  GDR_CHECK_ARG(m2 && y2, GDR_E_BADARG, "spmm_dual: m2 / y2 missing");
+  return spmm_f32_impl(rowptr, col, val, n_rows, d, x, nullptr, e1, e2, y, m2, y2, hub_threshold, n_hubs, hub_info,
+                       n_chunks, chunk_info, tickets, partial, stream);
 }
 
 int gdr_spmm_csr_f32(const int32_t *rowptr, const int32_t *col, const float *val, int64_t n_rows, int64_t d,

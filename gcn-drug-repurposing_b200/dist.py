@@ -173,53 +173,71 @@ def coarse_histogram(row_global, col_global, n, bins):
     return torch.bincount(key, minlength=bins * bins).reshape(bins, bins), size
 
 
-def lshape_bounds(hist, bin_size, n, parts, row_weight=6.0):
+def lshape_bounds(hist, bin_size, n, parts, row_weight=6.0, comm_weight=0.0):
     """Bounds [parts+1] (multiples of bin_size, last = n) that minimise the largest L-shape cost
         cost(s) = nnz(L_s) + row_weight * (own rows + expected non-empty rows of the push blocks computed here
-                                           + add pass: own rows + expected partial rows received),
-    by bisection on the cost cap with a greedy left-to-right fill.  hist: numpy [B, B] from
-    coarse_histogram (summed over ranks)."""
+                                           + add pass: own rows + expected partial rows received)
+                           + comm_weight * max(rows sent, rows received)      (X rows and partial rows together)
+    by bisection on the cost cap with a greedy left-to-right fill.  All row counts are Poisson estimates from the
+    coarse histogram (rows of a bin hit by lambda entries each: non-empty fraction 1 - exp(-lambda)); for traffic
+    towards the not-yet-placed higher ranks the remaining index range is taken as (parts - s - 1) equal chunks.
+    comm_weight is in nnz-equivalents per row moved (a 512-byte row at ~750 GB/s costs ~14 gathers of ~50 ps).
+    hist: numpy [B, B] from coarse_histogram (summed over ranks)."""
     hist = np.asarray(hist, dtype=np.float64)
     nb = hist.shape[0]
     sq = np.zeros(nb + 1)
     sq[1:] = np.diagonal(hist.cumsum(0).cumsum(1))                      # nnz of the leading square [0,b)x[0,b)
     ccum = np.zeros((nb, nb + 1))
     ccum[:, 1:] = hist.cumsum(1)                                         # per row bin, cumulative over columns
+    rcum = np.zeros((nb + 1, nb))
+    rcum[1:, :] = hist.cumsum(0)                                         # per column bin, cumulative over rows
     rows_in = np.minimum(np.arange(1, nb + 1) * bin_size, n) - np.minimum(np.arange(nb) * bin_size, n)
+    rows_in = np.maximum(rows_in, 1).astype(np.float64)
 
-    def costs_from(b0):
-        """cost of an L-shape starting at bin b0 for every end bin b1 in (b0, nb]  -> array [nb - b0]."""
+    def hit(lam_total, rows, chunks=1):
+        """expected (row, chunk) pairs with at least one entry, lam_total entries spread over rows x chunks"""
+        return rows * chunks * (1.0 - np.exp(-lam_total / (rows * chunks)))
+
+    def costs_from(b0, s):
+        """cost of rank s's L-shape starting at bin b0, for every end bin b1 in (b0, nb]  -> array [nb - b0]."""
+        w = nb - b0
         ends = np.arange(b0 + 1, nb + 1)
         c = sq[ends] - sq[b0]
         own = np.minimum(ends * bin_size, n) - min(b0 * bin_size, n)
+        inside = np.triu(np.ones((w, w)))                                # [bin offset i, end offset e]: i < end
         if b0 > 0:
-            lam = (ccum[:b0, b0 + 1:nb + 1] - ccum[:b0, b0:b0 + 1]) / np.maximum(rows_in[:b0, None], 1)
-            push_rows = (rows_in[:b0, None] * (1.0 - np.exp(-lam))).sum(0)
+            lam = ccum[:b0, b0 + 1:nb + 1] - ccum[:b0, b0:b0 + 1]       # rows of lower ranks x columns [b0, end)
+            push_rows = hit(lam, rows_in[:b0, None]).sum(0)              # partial rows computed here and sent down
+            low = rcum[b0 + 1:nb + 1, :b0].T - rcum[b0:b0 + 1, :b0].T    # [col bin < b0, end]: rows [b0, end)
+            recv_x = hit(low, rows_in[:b0, None]).sum(0)                 # X rows pulled from lower ranks
         else:
-            push_rows = 0.0
-        # add pass of this rank: partial rows arrive for its rows that have entries right of the block
-        right = ccum[b0:, nb:nb + 1] - ccum[b0:, b0 + 1:nb + 1]            # [row bin >= b0, end bin]: nnz in cols >= end
-        lam_r = right / np.maximum(rows_in[b0:, None], 1)
-        got = rows_in[b0:, None] * (1.0 - np.exp(-lam_r))                   # expected rows with a partial, per row bin
-        tri = np.tril(np.ones((nb - b0, nb - b0)), 0).T                     # row bin i (offset) counts for ends > i
-        recv_rows = (got * tri).sum(0)
-        add = np.where(recv_rows > 0, own + recv_rows, 0.0)
-        return np.maximum.accumulate(c + row_weight * (own + push_rows + add))
+            push_rows, recv_x = 0.0, 0.0
+        m = max(parts - s - 1, 1)
+        right = ccum[b0:, nb:nb + 1] - ccum[b0:, b0 + 1:nb + 1]          # [row bin >= b0, end]: nnz in cols >= end
+        recv_p = (hit(right, rows_in[b0:, None], m) * inside).sum(0)     # partial rows received from higher ranks
+        recv_rows = (hit(right, rows_in[b0:, None]) * inside).sum(0)     # distinct own rows that receive any
+        below = rcum[nb:nb + 1, b0:].T - rcum[b0 + 1:nb + 1, b0:].T      # [col bin >= b0, end]: nnz in rows >= end
+        sent_x = (hit(below, rows_in[b0:, None], m) * inside).sum(0)     # X rows pushed up to higher ranks
+        if s == parts - 1:
+            recv_p, sent_x, recv_rows = 0.0 * recv_p, 0.0 * sent_x, 0.0 * recv_rows
+        add = np.where(recv_rows > 0, own + recv_p, 0.0)
+        comm = np.maximum(sent_x + push_rows, recv_x + recv_p)
+        return np.maximum.accumulate(c + row_weight * (own + push_rows + add) + comm_weight * comm)
 
     def fill(cap):
         b, out = 0, [0]
-        for _ in range(parts):
+        for s in range(parts):
             if b >= nb:
                 out.append(nb)
                 continue
-            c = costs_from(b)
+            c = costs_from(b, s)
             k = int(np.searchsorted(c, cap, side="right"))               # number of end bins with cost <= cap
             b = b + max(k, 1)
             out.append(min(b, nb))
         return out
 
-    lo, hi = 0.0, float(costs_from(0)[-1])
-    for _ in range(40):
+    lo, hi = 0.0, float(costs_from(0, 0)[-1]) * 1.01 + 1.0
+    for _ in range(30):
         mid = 0.5 * (lo + hi)
         if fill(mid)[-1] >= nb:
             hi = mid
@@ -412,6 +430,13 @@ class LShapedSpMM:
                                                       _ffi.ptr(self.xsend), _ffi.stream()), "gather_rows")
         dist.all_to_all_single(self.x_recv, self.xsend, self.xrecv_splits, self.xsend_splits, group=self.group)
 
+    def push_product(self):
+        if self.n_psend:
+            self.push.spmm(self.x_own, out=self.psend)                    # needs only the own X block
+
+    def hub_reduce(self):
+        pass                                                              # (NvlsLShapedSpMM only)
+
     def exchange_partials(self):
         if self.p2p:
             torch.cuda.current_stream().wait_event(self._ev_b0)
@@ -432,8 +457,7 @@ class LShapedSpMM:
         with torch.cuda.stream(cs):
             self.exchange_x()
             ev_x = cs.record_event()
-        if self.n_psend:
-            self.push.spmm(self.x_own, out=self.psend)                    # needs only the own X block
+        self.push_product()
         ev_p = cur.record_event()
         with torch.cuda.stream(cs2):
             cs2.wait_event(ev_p)
@@ -445,4 +469,223 @@ class LShapedSpMM:
         cur.wait_event(ev_y)
         if self.n_precv:
             self.add.spmm(self.precv, e1=self.y, out=self.y)              # fixed (row, source rank) order
+        return self.y
+
+
+class NvlsLShapedSpMM:
+    """L-shaped partition whose lowest `n_hubs` ranks ("hub ranks": on a skewed graph their rows/columns are the
+    ones everybody references) exchange through NVSwitch multicast instead of unicast rows:
+
+      X rows of a hub rank    one multimem.st broadcast of its whole block into the same symmetric region on every
+                              GPU (gdr_mc_broadcast_f32): the block leaves the hub once, the switch fans it out;
+                              every pull matrix addresses hub columns directly in that replica.
+      partial rows FOR a hub  every higher rank writes the dense product of its block (hub rows x own columns) into
+                              the same symmetric region locally; the hub adds all of them with ONE multimem.ld_reduce
+                              pass (gdr_mc_reduce_add_f32): the sum is formed in the switch, the hub receives each
+                              of its rows once instead of once per sender.
+    Non-hub traffic stays unicast peer stores (gdr_push_rows_f32) exactly as in LShapedSpMM(transport="p2p").
+    Measured motivation (R-MAT scale 24, p = 8): rank 0 owns 1.72 M rows but has to send 5.58 M row copies and
+    receive 5.58 M partial rows, 2-3x any other rank - its NVLink port is the step's critical path.
+
+    Symmetric buffer, same row offsets on every rank:
+      [HUBP Hrows | PSEND psend_max | HUBX Hrows | XOWN own_max | XRECV xrecv_max | PRECV precv_max]
+    push output = [HUBP | PSEND) (contiguous), pull input V = [HUBX .. PRECV) (column ids are V-relative)."""
+
+    def __init__(self, local_csr, bounds, rank, world, d, n_hubs=1, group=None, push_ctas=0):
+        import ctypes
+        import torch.distributed._symmetric_memory as symm
+        self.bounds = [int(b) for b in bounds]
+        self.rank, self.world, self.d, self.group = rank, world, d, group
+        nh = self.n_hubs = max(1, min(int(n_hubs), world - 1))
+        self.push_ctas = int(push_ctas)
+        dev = local_csr.device
+        s = rank
+        lo, hi = self.bounds[s], self.bounds[s + 1]
+        self.n, self.n_own = self.bounds[-1], hi - lo
+        self.is_hub = s < nh
+        bnd = torch.tensor(self.bounds, dtype=torch.int64, device=dev)
+        own_rows = [self.bounds[r + 1] - self.bounds[r] for r in range(world)]
+        hub_off = [sum(own_rows[:h]) for h in range(nh)]                  # row offset of hub h inside HUBX / HUBP
+        Hrows = sum(own_rows[:nh])
+        hub_off_t = torch.tensor(hub_off + [0] * (world - nh), dtype=torch.int64, device=dev)
+        col = local_csr.col.to(torch.int64)
+        deg = (local_csr.rowptr[1:] - local_csr.rowptr[:-1]).to(torch.int64)
+        row = torch.repeat_interleave(torch.arange(self.n_own, device=dev), deg)
+        owner = torch.searchsorted(bnd, col, right=True) - 1
+        val = local_csr.val
+
+        # ---- pull part (columns owned by ranks <= s): which rows still travel unicast ---------------------
+        keep = owner <= s
+        kcol, krow, kval, kown = col[keep], row[keep], val[keep], owner[keep]
+        k_hub = kown < nh
+        k_self = (kown == s) & ~k_hub
+        k_rem = ~k_hub & ~k_self
+        remote = torch.unique(kcol[k_rem])                                # sorted => grouped by (non-hub) owner
+        cut = torch.searchsorted(remote, bnd)
+        need_from = [remote[int(cut[r]):int(cut[r + 1])] - self.bounds[r] for r in range(world)]
+        self.xrecv_splits = [int(t.numel()) for t in need_from]
+        n_xrecv = int(sum(self.xrecv_splits))
+        want = torch.cat(need_from) if n_xrecv else torch.zeros(0, dtype=torch.int64, device=dev)
+        self.send_idx, self.xsend_splits = _a2a_var(want, self.xrecv_splits, group)
+
+        # ---- push part: entries above the diagonal go to their column owner, once --------------------------
+        up = ~keep
+        uo = owner[up]
+        order = torch.argsort(uo, stable=True)
+        cnt = torch.bincount(uo, minlength=world).tolist()
+        g_row, _ = _a2a_var((row[up] + lo)[order], cnt, group)
+        g_col, _ = _a2a_var(col[up][order], cnt, group)
+        g_val, _ = _a2a_var(val[up][order], cnt, group)                    # grouped by source rank, row-major inside
+        g_src = torch.searchsorted(bnd, g_row, right=True) - 1             # the row owner = the source rank
+        to_hub = g_src < nh
+        rows_u, inv = torch.unique(g_row[~to_hub], return_inverse=True)    # compact rows for non-hub owners
+        self.n_psend = int(rows_u.numel())
+        prow = torch.empty_like(g_row)
+        prow[to_hub] = hub_off_t[g_src[to_hub]] + (g_row[to_hub] - bnd[g_src[to_hub]])   # dense inside HUBP
+        prow[~to_hub] = Hrows + inv
+        self.push = csr_from_sorted_rows(prow, g_col - lo, g_val, Hrows + self.n_psend, self.n_own)
+        cut = torch.searchsorted(rows_u, bnd)
+        self.psend_splits = [int(cut[a + 1] - cut[a]) for a in range(world)]
+        back = rows_u - bnd[torch.searchsorted(bnd, rows_u, right=True) - 1]
+        add_rows, self.precv_splits = _a2a_var(back, self.psend_splits, group)
+        self.n_precv = int(add_rows.numel())
+        pos = torch.arange(self.n_precv, device=dev)
+        o2 = torch.argsort(add_rows, stable=True)
+        self.add = csr_from_sorted_rows(add_rows[o2], pos[o2], torch.ones(self.n_precv, dtype=val.dtype, device=dev),
+                                        self.n_own, max(self.n_precv, 1))
+
+        # ---- the symmetric buffer -----------------------------------------------------------------------------
+        meta = [None] * world
+        dist.all_gather_object(meta, dict(xrecv=self.xrecv_splits, precv=self.precv_splits, psend=self.n_psend),
+                               group=group)
+        psend_max = max(max(m["psend"] for m in meta), 1)
+        own_max = max(own_rows[nh:]) if world > nh else 1
+        xrecv_max = max(max(sum(m["xrecv"]) for m in meta), 1)
+        precv_max = max(max(sum(m["precv"]) for m in meta), 1)
+        A0 = 0
+        B0 = A0 + Hrows
+        C0 = B0 + psend_max
+        D0 = C0 + Hrows
+        E0 = D0 + own_max
+        F0 = E0 + xrecv_max
+        total = F0 + precv_max
+        self._symm_t = symm.empty(total * d, dtype=val.dtype, device=dev)
+        self._hdl = symm.rendezvous(self._symm_t, (group or dist.group.WORLD).group_name)
+        mc = int(getattr(self._hdl, "multicast_ptr", 0) or 0)
+        if mc == 0:
+            raise RuntimeError("NvlsLShapedSpMM: this system exposes no NVSwitch multicast mapping (NVLS)")
+        self._symm_t.zero_()                                               # HUBP regions nobody writes must read as 0
+        buf = self._symm_t.view(total, d)
+        esz = self._symm_t.element_size()
+        rowb = d * esz
+        self.push_out = buf[A0:A0 + Hrows + self.n_psend]
+        self.psend = buf[B0:B0 + self.n_psend]
+        self.xbuf = buf[C0:F0]                                             # V: what the pull matrix gathers from
+        self.x_own = buf[C0 + hub_off[s]:C0 + hub_off[s] + self.n_own] if self.is_hub else buf[D0:D0 + self.n_own]
+        self.x_recv = buf[E0:E0 + n_xrecv]
+        self.precv = buf[F0:F0 + self.n_precv]
+        self.y = torch.empty(self.n_own, d, dtype=val.dtype, device=dev)
+        self._mc_hubx = mc + (C0 + (hub_off[s] if self.is_hub else 0)) * rowb
+        self._mc_hubp = mc + (A0 + (hub_off[s] if self.is_hub else 0)) * rowb
+
+        # pull matrix with V-relative columns
+        new_col = torch.empty_like(kcol)
+        new_col[k_hub] = hub_off_t[kown[k_hub]] + (kcol[k_hub] - bnd[kown[k_hub]])
+        new_col[k_self] = (D0 - C0) + (kcol[k_self] - lo)
+        new_col[k_rem] = (E0 - C0) + torch.searchsorted(remote, kcol[k_rem])
+        self.pull = csr_from_sorted_rows(krow, new_col, kval, self.n_own, F0 - C0)
+        self.needs_remote_x = bool((k_rem.any() | (k_hub & (kown != s)).any()).item())
+
+        # unicast destination tables
+        base = [int(p) for p in self._hdl.buffer_ptrs]
+        arr, i64 = ctypes.c_void_p * world, ctypes.c_int64 * world
+        xdst, xidx, xcnt, off = [None] * world, [None] * world, [0] * world, 0
+        for r in range(world):
+            c = self.xsend_splits[r]
+            if c:
+                xdst[r] = base[r] + (E0 + sum(meta[r]["xrecv"][:s])) * rowb
+                xidx[r] = self.send_idx.data_ptr() + off * 8
+                xcnt[r] = c
+            off += c
+        self._xpush = (arr(*xdst), arr(*xidx), i64(*([0] * world)), i64(*xcnt))
+        pdst, pcnt, poff, off = [None] * world, [0] * world, [0] * world, 0
+        for a in range(world):
+            c = self.psend_splits[a]
+            if c:
+                pdst[a] = base[a] + (F0 + sum(meta[a]["precv"][:s])) * rowb
+                poff[a], pcnt[a] = off, c
+            off += c
+        self._ppush = (arr(*pdst), arr(*([None] * world)), i64(*poff), i64(*pcnt))
+
+        self.recv_rows = n_xrecv + self.n_precv + (0 if self.is_hub else Hrows)
+        self.comm_stream = torch.cuda.Stream(device=dev, priority=-1)
+        self.comm_stream2 = torch.cuda.Stream(device=dev, priority=-1)
+        self.transport = ("NVSwitch multicast for the %d hub rank(s) (multimem.st broadcast of their X block, "
+                          "multimem.ld_reduce of their partial rows) + p2p stores into peer symmetric memory for the "
+                          "rest, L-shaped partition" % nh)
+        torch.cuda.synchronize()
+        self._hdl.barrier(channel=3)                                       # everyone's zero fill is done
+        torch.cuda.synchronize()
+
+    @classmethod
+    def from_full(cls, full_csr, bounds, rank, world, d, **kw):
+        lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+        p0, p1 = int(full_csr.rowptr[lo].item()), int(full_csr.rowptr[hi].item())
+        local = DeviceCSR((full_csr.rowptr[lo:hi + 1] - p0).contiguous(), full_csr.col[p0:p1].clone(),
+                          full_csr.val[p0:p1].clone(), hi - lo, full_csr.n_cols)
+        return cls(local, bounds, rank, world, d, **kw)
+
+    def _push(self, src, table):
+        dst, idx, off, cnt = table
+        _ffi.check(_ffi.lib().gdr_push_rows_f32(_ffi.ptr(src) if src.numel() else None, self.d, self.world, dst, idx,
+                                                off, cnt, self.push_ctas, _ffi.stream()), "push_rows")
+
+    def exchange_x(self):
+        self._hdl.barrier(channel=0)                 # every rank is done with last step's buffers
+        self._ev_b0 = torch.cuda.current_stream().record_event()
+        if self.is_hub:
+            _ffi.check(_ffi.lib().gdr_mc_broadcast_f32(_ffi.ptr(self.x_own), self._mc_hubx, self.n_own * self.d,
+                                                       self.push_ctas, _ffi.stream()), "mc_broadcast")
+        elif self.send_idx.numel():
+            self._push(self.x_own, self._xpush)
+        self._hdl.barrier(channel=1)                 # every replica and every pushed row has landed
+
+    def push_product(self):
+        if self.push.nnz:
+            self.push.spmm(self.x_own, out=self.push_out)      # dense hub partials | compact rows for the others
+
+    def exchange_partials(self):
+        torch.cuda.current_stream().wait_event(self._ev_b0)
+        if self.n_psend:
+            self._push(self.psend, self._ppush)
+        self._hdl.barrier(channel=2)                 # all partial rows are in place (HUBP locally, PRECV remotely)
+
+    def hub_reduce(self):
+        if self.is_hub:
+            _ffi.check(_ffi.lib().gdr_mc_reduce_add_f32(_ffi.ptr(self.y), self._mc_hubp, self.n_own * self.d, 0,
+                                                        _ffi.stream()), "mc_reduce_add")
+
+    def spmm(self, x_local=None):
+        if x_local is not None and x_local.data_ptr() != self.x_own.data_ptr():
+            self.x_own.copy_(x_local)
+        cur = torch.cuda.current_stream()
+        cs, cs2 = self.comm_stream, self.comm_stream2
+        cs.wait_stream(cur)
+        with torch.cuda.stream(cs):
+            self.exchange_x()
+            ev_x = cs.record_event()
+        cur.wait_event(self._ev_b0)                  # HUBP / PSEND of the previous step were consumed everywhere
+        self.push_product()
+        ev_p = cur.record_event()
+        with torch.cuda.stream(cs2):
+            cs2.wait_event(ev_p)
+            self.exchange_partials()
+            ev_y = cs2.record_event()
+        if self.needs_remote_x:
+            cur.wait_event(ev_x)
+        self.pull.spmm(self.xbuf, out=self.y)
+        cur.wait_event(ev_y)
+        if self.n_precv:
+            self.add.spmm(self.precv, e1=self.y, out=self.y)
+        self.hub_reduce()
         return self.y

@@ -179,8 +179,9 @@ class DeviceCSR:
         return self._plan or None
 
     # ---- SpMM ------------------------------------------------------------------------------------
-    def spmm(self, x, mul=None, e1=None, e2=None, out=None):
-        """out = self · x  (gathered operand x ⊙ mul if mul is given; + e1 ⊙ e2 if given)."""
+    def spmm(self, x, mul=None, e1=None, e2=None, out=None, out2_mul=None, out2=None):
+        """out = self · x  (gathered operand x ⊙ mul if mul is given; + e1 ⊙ e2 if given).
+        out2_mul: also return out2 = out ⊙ out2_mul from the same launch (fp32, no `mul`); returns (out, out2)."""
         L = _ffi.lib()
         if x.dim() != 2 or x.shape[0] != self.n_cols:
             raise RuntimeError(f"spmm: x has shape {tuple(x.shape)}, adjacency is {self.n_rows}x{self.n_cols}")
@@ -193,7 +194,22 @@ class DeviceCSR:
         if rec is not None:
             ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
             ev0.record()
-        if x.dtype == torch.float32:
+        if out2_mul is not None:
+            if x.dtype != torch.float32 or mul is not None:
+                raise RuntimeError("spmm: the second output is fp32-only and excludes a gathered multiplier")
+            if out2 is None:
+                out2 = torch.empty_like(out)
+            pl = self.plan()
+            if pl is not None and (pl["partial"] is None or pl["partial"].shape[1] != d):
+                pl["partial"] = torch.empty(pl["n_chunks"], d, dtype=torch.float32, device=x.device)
+            _ffi.check(L.gdr_spmm_csr_dual_f32(
+                _ffi.ptr(self.rowptr), _ffi.ptr(self.col), _ffi.ptr(self.val), self.n_rows, d, _ffi.ptr(x),
+                _ffi.ptr(e1), _ffi.ptr(e2), _ffi.ptr(out), _ffi.ptr(out2_mul), _ffi.ptr(out2),
+                self.HUB_THRESHOLD if pl else 0, pl["n_hubs"] if pl else 0, _ffi.ptr(pl["hub_info"]) if pl else None,
+                pl["n_chunks"] if pl else 0, _ffi.ptr(pl["chunk_info"]) if pl else None,
+                _ffi.ptr(pl["tickets"]) if pl else None, _ffi.ptr(pl["partial"]) if pl else None, _ffi.stream()),
+                "spmm_csr_dual_f32")
+        elif x.dtype == torch.float32:
             pl = self.plan()
             if pl is None:
                 _ffi.check(L.gdr_spmm_csr_f32(_ffi.ptr(self.rowptr), _ffi.ptr(self.col), _ffi.ptr(self.val),
@@ -217,6 +233,8 @@ class DeviceCSR:
         if rec is not None:
             ev1.record()
             rec.append((ev0, ev1, self.nnz, self.n_rows, d, mul is not None, e1 is not None))
+        if out2_mul is not None:
+            return out, out2
         return out
 
 

@@ -45,8 +45,9 @@ def layer_forward_raw(csr, x, w1, b1, w2, b2, residual, decay):
     Returns P = Â·x, T = Â·(P⊙x), Z (pre-nonlinearity), Xnext (= ELU(Z) or residual + decay*ELU(Z))."""
     L = _ffi.lib()
     n, d = x.shape
-    p = csr.spmm(x)                      # model.py:163
-    t = csr.spmm(p, mul=x)               # model.py:168-169 (torch.mul folded into the gather)
+    p, px = csr.spmm(x, out2_mul=x)      # model.py:163, and torch.mul(P, X) of :168 from the same launch
+    t = csr.spmm(px)                     # model.py:169
+    del px
     z = torch.empty_like(x)
     xnext = torch.empty_like(x)
     if GEMM_BACKEND == "tc":

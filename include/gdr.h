@@ -105,6 +105,14 @@ int gdr_spmm_csr_planned_f32(const int32_t *rowptr, const int32_t *col, const fl
                              int64_t n_hubs, const int32_t *hub_info, int64_t n_chunks,
                              const int32_t *chunk_info, int32_t *tickets, float *partial,
                              gdr_stream_t stream);
+/* y = Â·x (+ e1 ⊙ e2) and, from the same launch, y2 = y ⊙ m2 (m2, y2 row-aligned with y).  The layer
+ * needs both P = Â·X and torch.mul(P, X) (modules/model.py:163,168): writing the product here makes the
+ * following T = Â·(P ⊙ X) a one-operand gather.  Plan arguments as in gdr_spmm_csr_planned_f32.       */
+int gdr_spmm_csr_dual_f32(const int32_t *rowptr, const int32_t *col, const float *val, int64_t n_rows,
+                          int64_t d, const float *x, const float *e1, const float *e2, float *y,
+                          const float *m2, float *y2, int32_t hub_threshold, int64_t n_hubs,
+                          const int32_t *hub_info, int64_t n_chunks, const int32_t *chunk_info,
+                          int32_t *tickets, float *partial, gdr_stream_t stream);
 int gdr_spmm_csr_f64(const int32_t *rowptr, const int32_t *col, const double *val,
                      int64_t n_rows, int64_t d, const double *x, double *y,
                      gdr_stream_t stream);
@@ -195,6 +203,11 @@ int gdr_gather_rows_f32(const float *src, const int64_t *index, int64_t b, int64
  * gdr_gather_rows_f32 + ncclSend of the packed buffer.  n_ctas <= 0: default.                            */
 int gdr_push_rows_f32(const float *src, int64_t d, int n_dst, float *const *dst, const int64_t *const *idx,
                       const int64_t *src_off, const int64_t *counts, int n_ctas, gdr_stream_t stream);
+/* NVSwitch multicast (NVLS) forms of the two hub exchanges; mc_* are multicast addresses of a symmetric
+ * allocation (multimem.st / multimem.ld_reduce).  broadcast: the hub block of X reaches every GPU while leaving
+ * this one once.  reduce_add: y += the sum over all GPUs of their partial-row buffers, reduced in the switch.  */
+int gdr_mc_broadcast_f32(const float *src, float *mc_dst, int64_t count, int n_ctas, gdr_stream_t stream);
+int gdr_mc_reduce_add_f32(float *y, const float *mc_src, int64_t count, int n_ctas, gdr_stream_t stream);
 /* gh[index[i],:] += scale_dev[0] * ge[i,:]  (autograd of embs[index]); gh pre-zeroed. */
 int gdr_scatter_rows_f32(const float *ge, const int64_t *index, int64_t b, int64_t n,
                          int64_t d, const float *scale_dev, float *gh, gdr_stream_t stream);
