@@ -58,6 +58,8 @@ def parse_args():
     p.add_argument("--hubs", type=int, default=0,
                    help="N>1, lshape: the lowest K ranks exchange through NVSwitch multicast (multimem broadcast of "
                         "their X block, in-switch reduction of their partial rows)")
+    p.add_argument("--no-refine", action="store_true",
+                   help="N>1, lshape: keep the cost-cap bounds (skip the descent on the step timeline model)")
     p.add_argument("--comm-weight", type=float, default=0.0,
                    help="N>1, lshape: cost of one row moved, in nnz-equivalents, in the partition's balance")
     p.add_argument("--two-comms", action="store_true", help="N>1, lshape: partial rows on a second NCCL communicator")
@@ -411,8 +413,11 @@ def run_rmat_spmm_dist(args):
         row_of = torch.repeat_interleave(torch.arange(n, device=dev), deg)
         hist, bin_size = gdist.coarse_histogram(row_of, full.col.to(torch.int64), n, min(1024, n))
         del row_of, deg
-        bounds = gdist.lshape_bounds(hist.cpu().numpy(), bin_size, n, world, row_weight=args.row_weight,
+        hist_np = hist.cpu().numpy()
+        bounds = gdist.lshape_bounds(hist_np, bin_size, n, world, row_weight=args.row_weight,
                                      comm_weight=args.comm_weight)
+        if not args.no_refine:
+            bounds, _pred = gdist.refine_lshape_bounds(hist_np, bin_size, n, bounds, d)
     else:
         rp = full.rowptr.cpu().numpy().astype(np.int64)
         bounds = gdist.nnz_balanced_bounds(rp + (np.arange(len(rp)) * args.row_weight).astype(np.int64), world)
@@ -513,6 +518,33 @@ def run_rmat_spmm_dist(args):
     launches = torch.tensor([gdr._ffi.launch_count()], device=dev, dtype=torch.int64)
     dist.all_reduce(launches)
     ms = float(ms.item())
+    # ---- end-to-end arm: the rank's X block comes from pinned host memory and its Y block goes back to it,
+    # every step, inside the timed region (host buffers through the public call) --------------------------------
+    x_host = torch.empty(part.x_own.shape, dtype=torch.float32).pin_memory()
+    x_host.copy_(part.x_own)
+    y_host = torch.empty(part.y.shape, dtype=torch.float32).pin_memory()
+    e2e_steps = max(2, min(args.steps, 4))
+
+    def e2e_step():
+        part.x_own.copy_(x_host, non_blocking=True)
+        yb = part.spmm(None)
+        y_host.copy_(yb, non_blocking=True)
+
+    e2e_step()
+    torch.cuda.synchronize()
+    dist.barrier()
+    f0, f1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    f0.record()
+    for _ in range(e2e_steps):
+        e2e_step()
+    f1.record()
+    torch.cuda.synchronize()
+    dist.barrier()
+    e2e_ms = torch.tensor([f0.elapsed_time(f1) / e2e_steps], device=dev, dtype=torch.float64)
+    dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
+    io = torch.tensor([x_host.numel() * 4, y_host.numel() * 4], device=dev, dtype=torch.int64)
+    dist.all_reduce(io)
+    e2e_ms = float(e2e_ms.item())
     line = None
     if rank == 0:
         clk = clocks.stop()
@@ -533,7 +565,10 @@ def run_rmat_spmm_dist(args):
                        "l2": "inputs larger than L2", "transport": part.transport,
                        "rows_received_per_rank_rank0": part.recv_rows,
                        "check_vs_1gpu_product": {"within_tolerance": tol_ok, "max_abs_err": max_err}},
-            "e2e": None, "gpu_launches": int(launches.item()), "clocks": clk,
+            "e2e": {"value": nnz_total / (e2e_ms * 1e-3) / 1e9, "unit": "GEdges/s", "ms_per_step": e2e_ms,
+                    "steps": e2e_steps, "h2d_bytes_per_step": int(io[0].item()), "d2h_bytes_per_step": int(io[1].item()),
+                    "note": "every rank uploads its X block from pinned host memory and downloads its Y block, each step"},
+            "gpu_launches": int(launches.item()), "clocks": clk,
             "roofline": {"kernel": "spmm_warp_row_kernel<float> + all-gather", "bound": "hbm",
                          "achieved": gbs, "peak": peak * world, "unit": "GB/s", "frac": gbs / (peak * world),
                          "traffic": None, "peak_source": peak_src + f" x{world} GPUs",

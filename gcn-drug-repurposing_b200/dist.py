@@ -689,3 +689,78 @@ class NvlsLShapedSpMM:
             self.add.spmm(self.precv, e1=self.y, out=self.y)
         self.hub_reduce()
         return self.y
+
+
+# ---- a timeline model of one L-shaped step, used to refine the bounds ------------------------------------------
+# Constants measured on B200 / NVLink 5 (profiles/diag_r1_n8_lshape_hubs0.txt): seconds per gathered entry, per
+# output row written by an SpMM, per row touched by the add pass, and per 512-byte row moved over one NVSwitch port.
+STEP_MODEL = dict(t_nnz=50e-12, t_row=250e-12, t_add=235e-12, link_bytes_per_s=695e9, t_sync=0.15e-3)
+
+
+def lshape_step_model(hist, bin_size, n, bbins, d, consts=None):
+    """Predicted step time [s] and per-rank detail for L-shape bounds given in bins (bbins[0] = 0, bbins[-1] = B).
+    Block (r, s) is multiplied by rank max(r, s); volumes are Poisson estimates from the coarse histogram."""
+    k = dict(STEP_MODEL, **(consts or {}))
+    hist = np.asarray(hist, dtype=np.float64)
+    nb = hist.shape[0]
+    p = len(bbins) - 1
+    rows_in = np.maximum(np.minimum(np.arange(1, nb + 1) * bin_size, n) - np.minimum(np.arange(nb) * bin_size, n), 1.0)
+    owner = np.searchsorted(np.asarray(bbins), np.arange(nb), side="right") - 1        # bin -> rank
+    own = np.array([rows_in[bbins[r]:bbins[r + 1]].sum() for r in range(p)])
+    nnz = np.zeros((p, p))
+    pullr = np.zeros((p, p))      # [r, s] r > s: distinct X rows of s that r references
+    pushr = np.zeros((p, p))      # [r, s] r < s: non-empty rows of block (r, s)
+    for r in range(p):
+        strip = hist[bbins[r]:bbins[r + 1], :]                                          # rows of r
+        col_tot = strip.sum(0)
+        hit_c = rows_in * (1.0 - np.exp(-col_tot / rows_in))                            # distinct columns per col bin
+        np.add.at(nnz[r], owner, col_tot)
+        np.add.at(pullr[r], owner, hit_c)
+        rr = rows_in[bbins[r]:bbins[r + 1]]
+        for s in range(r + 1, p):
+            lam = strip[:, bbins[s]:bbins[s + 1]].sum(1) / rr
+            pushr[r, s] = (rr * (1.0 - np.exp(-lam))).sum()
+    lower = np.tril(np.ones((p, p)), -1)
+    upper = lower.T
+    nnz_pull = (nnz * (lower + np.eye(p))).sum(1)
+    nnz_push = (nnz * upper).sum(0)
+    recv_x, sent_x = (pullr * lower).sum(1), (pullr * lower).sum(0)
+    recv_p, sent_p = (pushr * upper).sum(1), (pushr * upper).sum(0)
+    t_push = k["t_nnz"] * nnz_push + k["t_row"] * sent_p
+    t_pull = k["t_nnz"] * nnz_pull + k["t_row"] * own
+    t_add = np.where(recv_p > 0, k["t_add"] * (own + recv_p), 0.0)
+    rowb = d * 4.0
+    T_x = max(sent_x.max(), recv_x.max()) * rowb / k["link_bytes_per_s"] + k["t_sync"]
+    T_p = max(sent_p.max(), recv_p.max()) * rowb / k["link_bytes_per_s"] + k["t_sync"]
+    pull_start = np.where(recv_x > 0, np.maximum(t_push, T_x), t_push)
+    part_done = t_push.max() + T_p                        # one barrier: the slowest sender gates everybody
+    finish = np.maximum(pull_start + t_pull, np.where(recv_p > 0, part_done, 0.0)) + t_add
+    return float(finish.max()), dict(finish=finish, t_push=t_push, t_pull=t_pull, t_add=t_add, T_x=T_x, T_p=T_p,
+                                     sent_x=sent_x, recv_x=recv_x, sent_p=sent_p, recv_p=recv_p, own=own,
+                                     nnz_pull=nnz_pull, nnz_push=nnz_push)
+
+
+def refine_lshape_bounds(hist, bin_size, n, bounds, d, consts=None, sweeps=6):
+    """Coordinate descent on the interior bounds (in histogram bins) against lshape_step_model, starting from
+    `bounds` (rows).  Deterministic; every rank computes the same result from the same histogram."""
+    nb = np.asarray(hist).shape[0]
+    bb = [int(round(b / bin_size)) for b in bounds]
+    bb[0], bb[-1] = 0, nb
+    best, _ = lshape_step_model(hist, bin_size, n, bb, d, consts)
+    for _ in range(sweeps):
+        improved = False
+        for i in range(1, len(bb) - 1):
+            for step in (64, 16, 4, 1):
+                moved = True
+                while moved:
+                    moved = False
+                    for cand in (bb[i] - step, bb[i] + step):
+                        if bb[i - 1] < cand < bb[i + 1]:
+                            trial = bb[:i] + [cand] + bb[i + 1:]
+                            t, _ = lshape_step_model(hist, bin_size, n, trial, d, consts)
+                            if t < best * (1.0 - 1e-4):
+                                best, bb, moved, improved = t, trial, True, True
+                                break
+        if not improved:
+            break
+    return np.minimum(np.asarray(bb, dtype=np.int64) * bin_size, n), best

@@ -205,3 +205,25 @@ def test_lshape_bounds_balances_l_shapes():
     load = np.bincount(np.maximum(blk_r, blk_c), minlength=4)      # block (r, s) is computed by max(r, s)
     assert load.sum() == m.nnz and load.max() < 1.25 * m.nnz / 4, load
     assert gdist.lshape_bounds(hist.numpy(), size, 4000, 1).tolist() == [0, 4000]
+
+
+def test_step_model_and_refinement():
+    """The timeline model's volumes track the real ones, and the descent never worsens its own objective."""
+    import gdr_b200  # noqa: F401
+    from gdr_b200 import dist as gdist
+    n, p = 6000, 4
+    m = _skewed_matrix(n, 7).tocoo()
+    hist, size = gdist.coarse_histogram(torch.from_numpy(m.row.astype(np.int64)),
+                                        torch.from_numpy(m.col.astype(np.int64)), n, 200)
+    b0 = gdist.lshape_bounds(hist.numpy(), size, n, p, row_weight=2.0)
+    t0, det = gdist.lshape_step_model(hist.numpy(), size, n, [int(b // size) for b in b0], 128)
+    blk_r = np.searchsorted(b0, m.row, side="right") - 1
+    blk_c = np.searchsorted(b0, m.col, side="right") - 1
+    sent_x = np.zeros(p)
+    for r in range(p):
+        for s in range(r):
+            sent_x[s] += len(np.unique(m.col[(blk_r == r) & (blk_c == s)]))
+    assert np.allclose(det["sent_x"], sent_x, rtol=0.15, atol=30), (det["sent_x"], sent_x)
+    assert abs(det["nnz_pull"].sum() + det["nnz_push"].sum() - m.nnz) < 1e-6 * m.nnz
+    b1, t1 = gdist.refine_lshape_bounds(hist.numpy(), size, n, b0, 128)
+    assert t1 <= t0 * (1 + 1e-9) and b1[0] == 0 and b1[-1] == n and (np.diff(b1) > 0).all()
