@@ -286,11 +286,13 @@ int gdr_gcn_layer_fwd_tc_f32(const float *p, const float *t, const float *w1, co
   float *ahi = cv.take<float>(n * 2 * d), *alo = cv.take<float>(n * 2 * d);
   float *bhi = cv.take<float>(d * 2 * d), *blo = cv.take<float>(d * 2 * d);
   int rc;
-  if ((rc = tc_split(p, d, d, t, d, d, n, ahi, alo, st))) return rc;      // A = [P | T]   (n x 2d)
   if ((rc = tc_split(w1, d, d, w2, d, d, d, bhi, blo, st))) return rc;    // B = [W1 | W2] (d x 2d)
   GemmParams g{};
   g.c = z_out; g.ldc = d;
   g.bias1 = b1; g.bias2 = b2; g.residual = residual; g.decay = decay; g.xnext = xnext_out;
+  if (d % TC_K_ALIGN == 0)                                                 // A = [P | T], split inside the kernel
+    return tc_gemm_raw_a(EPI_LAYER, p, d, d, t, d, d, bhi, blo, 2 * d, n, d, g, st);
+  if ((rc = tc_split(p, d, d, t, d, d, n, ahi, alo, st))) return rc;      // odd widths: pre-split [P | T] (n x 2d)
   return tc_gemm(EPI_LAYER, ahi, alo, bhi, blo, n, d, 2 * d, 2 * d, 2 * d, 2 * d, 1, g, st);
 }
 
@@ -312,11 +314,11 @@ int gdr_linear_bwd_input_tc_f32(const float *g, const float *w, const float *e1,
   float *ahi = cv.take<float>(n * d), *alo = cv.take<float>(n * d);
   float *bhi = cv.take<float>(d * d), *blo = cv.take<float>(d * d);
   int rc;
-  if ((rc = tc_split(g, d, d, nullptr, 0, 0, n, ahi, alo, st))) return rc;   // A(m=node, k=out) = G
+  (void)ahi; (void)alo;                                                      // A(m=node, k=out) = G, split in-kernel
   if ((rc = tc_split_transpose(w, d, d, d, d, bhi, blo, st))) return rc;     // B(n=in, k=out)  = Wᵀ
   GemmParams q{};
   q.c = c_out; q.ldc = d; q.e1 = e1; q.e2 = e2;
-  return tc_gemm(EPI_STORE, ahi, alo, bhi, blo, n, d, d, d, d, d, 1, q, st);
+  return tc_gemm_raw_a(EPI_STORE, g, d, d, nullptr, 0, 0, bhi, blo, d, n, d, q, st);
 }
 
 static int tc_splits_for(int64_t n, int64_t d, int64_t *k_per_split) {

@@ -37,6 +37,7 @@ constexpr int TC_SMEM_BYTES = TC_STAGES * TC_STAGE_BYTES + 1024 /*alignment slac
 struct TcParams {
   int64_t m, n, k;         // k = full reduction length (all of it unless split-K)
   int64_t k_per_split;     // EPI_SPLITK: K range of blockIdx.z (multiple of TC_BK); otherwise >= k
+  int64_t k_a2;            // RAW_A: columns [k_a2, k) of A come from the second raw source (k_a2 % TC_BK == 0)
   GemmParams g;            // epilogue operands, same meaning as in gemm_simt.cuh (a/b/lda/ldb unused)
 };
 
@@ -158,7 +159,11 @@ __device__ __forceinline__ void tc_epilogue_row(const TcParams &p, int64_t m, in
   }
 }
 
-template <int EPI>
+// RAW_A: operand A arrives as plain fp32 (map_ahi = first source, map_alo = second source placed after it along
+// K) and is split into hi/lo in shared memory by the four epilogue warps while the pipeline runs: the TMA tile is
+// rewritten in place as hi, lo goes to the neighbouring slot, fence.proxy.async makes both visible to the
+// tensor core, and a `conv` mbarrier (128 arrivals) replaces `full` as the MMA issuer's go signal.
+template <int EPI, bool RAW_A>
 __global__ void __launch_bounds__(TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constant__ CUtensorMap map_alo,
                const __grid_constant__ CUtensorMap map_bhi, const __grid_constant__ CUtensorMap map_blo,
@@ -171,7 +176,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constan
   uint64_t *full = reinterpret_cast<uint64_t *>(smem + TC_STAGES * TC_STAGE_BYTES);
   uint64_t *empty = full + TC_STAGES;
   uint64_t *acc_ready = empty + TC_STAGES;
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_ready + 1);
+  uint64_t *conv = acc_ready + 1;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(conv + TC_STAGES);
   __shared__ unsigned int sh_hist[SYMMETRIC ? GHIST_BINS : 1];
   __shared__ double red[4];
 
@@ -190,6 +196,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constan
     for (int s = 0; s < TC_STAGES; ++s) {
       tc::mbar_init(&full[s], 1);
       tc::mbar_init(&empty[s], 1);
+      tc::mbar_init(&conv[s], 128);
     }
     tc::mbar_init(acc_ready, 1);
     tc::mbar_fence_init();
@@ -214,10 +221,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constan
         const uint32_t ph = (uint32_t)(kb / TC_STAGES) & 1u;
         tc::mbar_wait(&empty[s], ph ^ 1u);  // first lap passes immediately
         unsigned char *st = smem + s * TC_STAGE_BYTES;
-        tc::mbar_expect_tx(&full[s], TC_STAGE_BYTES);
+        tc::mbar_expect_tx(&full[s], RAW_A ? 3 * TC_TILE_BYTES : TC_STAGE_BYTES);
         const int32_t kc = (int32_t)(k_begin + (int64_t)kb * TC_BK);
-        tc::tma_load_2d(st + 0 * TC_TILE_BYTES, &map_ahi, &full[s], kc, (int32_t)m0);
-        tc::tma_load_2d(st + 1 * TC_TILE_BYTES, &map_alo, &full[s], kc, (int32_t)m0);
+        if (RAW_A) {
+          if (kc < p.k_a2)
+            tc::tma_load_2d(st + 0 * TC_TILE_BYTES, &map_ahi, &full[s], kc, (int32_t)m0);
+          else
+            tc::tma_load_2d(st + 0 * TC_TILE_BYTES, &map_alo, &full[s], kc - (int32_t)p.k_a2, (int32_t)m0);
+        } else {
+          tc::tma_load_2d(st + 0 * TC_TILE_BYTES, &map_ahi, &full[s], kc, (int32_t)m0);
+          tc::tma_load_2d(st + 1 * TC_TILE_BYTES, &map_alo, &full[s], kc, (int32_t)m0);
+        }
         tc::tma_load_2d(st + 2 * TC_TILE_BYTES, &map_bhi, &full[s], kc, (int32_t)n0);
         tc::tma_load_2d(st + 3 * TC_TILE_BYTES, &map_blo, &full[s], kc, (int32_t)n0);
       }
@@ -230,7 +244,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constan
       for (int kb = 0; kb < nkb; ++kb) {
         const int s = kb % TC_STAGES;
         const uint32_t ph = (uint32_t)(kb / TC_STAGES) & 1u;
-        tc::mbar_wait(&full[s], ph);
+        tc::mbar_wait(RAW_A ? &conv[s] : &full[s], ph);
         tc::tc_fence_after();
         unsigned char *st = smem + s * TC_STAGE_BYTES;
         const uint64_t d_ahi = tc::smem_desc_k_sw128(st + 0 * TC_TILE_BYTES);
@@ -256,6 +270,29 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constan
   } else {
     // ===== epilogue (warps 2..5; TMEM lane quarter = warp % 4) =====
     const int q = warp & 3;
+    if (RAW_A) {
+      const int t = threadIdx.x - 64;  // 0..127
+      for (int kb = 0; kb < nkb; ++kb) {
+        const int s = kb % TC_STAGES;
+        const uint32_t ph = (uint32_t)(kb / TC_STAGES) & 1u;
+        tc::mbar_wait(&full[s], ph);
+        float4 *hi4 = reinterpret_cast<float4 *>(smem + s * TC_STAGE_BYTES);
+        float4 *lo4 = reinterpret_cast<float4 *>(smem + s * TC_STAGE_BYTES + TC_TILE_BYTES);
+#pragma unroll
+        for (int i = 0; i < TC_TILE_BYTES / 16 / 128; ++i) {  // the swizzle is the same in both tiles
+          const float4 x = hi4[t + i * 128];
+          float4 h, l;
+          h.x = rn_tf32(x.x); l.x = rn_tf32(x.x - h.x);
+          h.y = rn_tf32(x.y); l.y = rn_tf32(x.y - h.y);
+          h.z = rn_tf32(x.z); l.z = rn_tf32(x.z - h.z);
+          h.w = rn_tf32(x.w); l.w = rn_tf32(x.w - h.w);
+          hi4[t + i * 128] = h;
+          lo4[t + i * 128] = l;
+        }
+        tc::fence_proxy_async();
+        tc::mbar_arrive(&conv[s]);
+      }
+    }
     tc::mbar_wait(acc_ready, 0u);
     tc::tc_fence_after();
     const int64_t m = m0 + q * 32 + lane;
@@ -341,30 +378,42 @@ static int make_operand_map(CUtensorMap *map, const float *base, int64_t rows, i
   return GDR_OK;
 }
 
-template <int EPI>
+// RAW_A: ahi = first raw source [m, k_a2] (lda), alo = second raw source [m, k - k_a2] (lda2) or nullptr
+template <int EPI, bool RAW_A>
 static int launch_gemm_tc(const float *ahi, const float *alo, const float *bhi, const float *blo, int64_t m, int64_t n,
                           int64_t k, int64_t lda, int64_t ldb, int64_t k_per_split, int splits, const GemmParams &g,
-                          cudaStream_t st) {
+                          cudaStream_t st, int64_t k_a2 = 0, int64_t lda2 = 0) {
+  int rc;
   if ((lda % 4) || (ldb % 4) || (((uintptr_t)ahi | (uintptr_t)alo | (uintptr_t)bhi | (uintptr_t)blo) & 15))
   {
     set_error("gemm_tc: operands must be 16-byte aligned with leading dimensions %% 4 == 0");
     return GDR_E_SHAPE;
   }
   CUtensorMap ma, ml, mb, mbl;
-  int rc;
-  if ((rc = make_operand_map(&ma, ahi, m, k, lda))) return rc;
-  if ((rc = make_operand_map(&ml, alo, m, k, lda))) return rc;
+  if (RAW_A) {
+    if (k_a2 <= 0 || k_a2 > k) k_a2 = k;
+    if (k_a2 < k && (!alo || (k_a2 % TC_BK) || (lda2 % 4))) {
+      set_error("gemm_tc: the second raw A source needs k_a2 %% %d == 0 and lda2 %% 4 == 0", TC_BK);
+      return GDR_E_SHAPE;
+    }
+    if ((rc = make_operand_map(&ma, ahi, m, k_a2, lda))) return rc;
+    if ((rc = make_operand_map(&ml, k_a2 < k ? alo : ahi, m, k_a2 < k ? k - k_a2 : k_a2, k_a2 < k ? lda2 : lda))) return rc;
+  } else {
+    if ((rc = make_operand_map(&ma, ahi, m, k, lda))) return rc;
+    if ((rc = make_operand_map(&ml, alo, m, k, lda))) return rc;
+  }
   if ((rc = make_operand_map(&mb, bhi, n, k, ldb))) return rc;
   if ((rc = make_operand_map(&mbl, blo, n, k, ldb))) return rc;
   TcParams p{};
-  p.m = m; p.n = n; p.k = k; p.k_per_split = k_per_split; p.g = g;
+  p.m = m; p.n = n; p.k = k; p.k_per_split = k_per_split; p.k_a2 = RAW_A ? k_a2 : k; p.g = g;
   static bool attr_set = false;  // per template instance
   if (!attr_set) {
-    GDR_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, TC_SMEM_BYTES));
+    GDR_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<EPI, RAW_A>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                  TC_SMEM_BYTES));
     attr_set = true;
   }
   dim3 grid((unsigned)ceil_div<int64_t>(n, TC_BN), (unsigned)ceil_div<int64_t>(m, TC_BM), (unsigned)splits);
-  gemm_tc_kernel<EPI><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(ma, ml, mb, mbl, p);
+  gemm_tc_kernel<EPI, RAW_A><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(ma, ml, mb, mbl, p);
   GDR_LAUNCHED();
   return GDR_OK;
 }
@@ -390,14 +439,28 @@ int tc_gemm(int epi, const float *ahi, const float *alo, const float *bhi, const
             int64_t k, int64_t lda, int64_t ldb, int64_t k_per_split, int splits, const GemmParams &g,
             cudaStream_t st) {
   switch (epi) {
-    case EPI_STORE: return launch_gemm_tc<EPI_STORE>(ahi, alo, bhi, blo, m, n, k, lda, ldb, k, 1, g, st);
-    case EPI_LAYER: return launch_gemm_tc<EPI_LAYER>(ahi, alo, bhi, blo, m, n, k, lda, ldb, k, 1, g, st);
-    case EPI_SPLITK: return launch_gemm_tc<EPI_SPLITK>(ahi, alo, bhi, blo, m, n, k, lda, ldb, k_per_split, splits, g, st);
-    case EPI_GSS: return launch_gemm_tc<EPI_GSS>(ahi, alo, bhi, blo, m, n, k, lda, ldb, k, 1, g, st);
-    case EPI_HIST: return launch_gemm_tc<EPI_HIST>(ahi, alo, bhi, blo, m, n, k, lda, ldb, k, 1, g, st);
-    case EPI_MINGT: return launch_gemm_tc<EPI_MINGT>(ahi, alo, bhi, blo, m, n, k, lda, ldb, k, 1, g, st);
+    case EPI_STORE: return launch_gemm_tc<EPI_STORE, false>(ahi, alo, bhi, blo, m, n, k, lda, ldb, k, 1, g, st);
+    case EPI_LAYER: return launch_gemm_tc<EPI_LAYER, false>(ahi, alo, bhi, blo, m, n, k, lda, ldb, k, 1, g, st);
+    case EPI_SPLITK: return launch_gemm_tc<EPI_SPLITK, false>(ahi, alo, bhi, blo, m, n, k, lda, ldb, k_per_split, splits, g, st);
+    case EPI_GSS: return launch_gemm_tc<EPI_GSS, false>(ahi, alo, bhi, blo, m, n, k, lda, ldb, k, 1, g, st);
+    case EPI_HIST: return launch_gemm_tc<EPI_HIST, false>(ahi, alo, bhi, blo, m, n, k, lda, ldb, k, 1, g, st);
+    case EPI_MINGT: return launch_gemm_tc<EPI_MINGT, false>(ahi, alo, bhi, blo, m, n, k, lda, ldb, k, 1, g, st);
   }
   set_error("gemm_tc: unknown epilogue %d", epi);
+  return GDR_E_BADARG;
+}
+
+int tc_gemm_raw_a(int epi, const float *a1, int64_t lda1, int64_t k1, const float *a2, int64_t lda2, int64_t k2,
+                  const float *bhi, const float *blo, int64_t ldb, int64_t m, int64_t n, const GemmParams &g,
+                  cudaStream_t st) {
+  const int64_t k = k1 + k2;
+  switch (epi) {
+    case EPI_STORE:
+      return launch_gemm_tc<EPI_STORE, true>(a1, a2, bhi, blo, m, n, k, lda1, ldb, k, 1, g, st, k1, lda2);
+    case EPI_LAYER:
+      return launch_gemm_tc<EPI_LAYER, true>(a1, a2, bhi, blo, m, n, k, lda1, ldb, k, 1, g, st, k1, lda2);
+  }
+  set_error("gemm_tc: raw-A form supports the store and layer epilogues only (got %d)", epi);
   return GDR_E_BADARG;
 }
 
@@ -426,11 +489,11 @@ int gdr_gemm_nt_tc_f32(const float *a, int64_t lda, const float *b, int64_t ldb,
   float *ahi = cv.take<float>(m * k), *alo = cv.take<float>(m * k);
   float *bhi = cv.take<float>(n * k), *blo = cv.take<float>(n * k);
   int rc;
-  if ((rc = tc_split(a, lda, k, nullptr, 0, 0, m, ahi, alo, st))) return rc;
+  (void)ahi; (void)alo;  // A is split inside the kernel
   if ((rc = tc_split(b, ldb, k, nullptr, 0, 0, n, bhi, blo, st))) return rc;
   GemmParams g{};
   g.c = c; g.ldc = ldc;
-  return tc_gemm(EPI_STORE, ahi, alo, bhi, blo, m, n, k, k, k, k, 1, g, st);
+  return tc_gemm_raw_a(EPI_STORE, a, lda, k, nullptr, 0, 0, bhi, blo, k, m, n, g, st);
 }
 
 }  // extern "C"

@@ -16,6 +16,12 @@ int tc_gemm(int epi, const float *ahi, const float *alo, const float *bhi, const
             int64_t k, int64_t lda, int64_t ldb, int64_t k_per_split, int splits, const GemmParams &g,
             cudaStream_t st);
 
+// the same with operand A as plain fp32, split inside the kernel: A = [a1 (k1 columns) | a2 (k2 columns)] along K
+// (a2 == nullptr, k2 == 0: one source).  Epilogues: EPI_STORE, EPI_LAYER.  k1 % 32 == 0 when a2 is given.
+int tc_gemm_raw_a(int epi, const float *a1, int64_t lda1, int64_t k1, const float *a2, int64_t lda2, int64_t k2,
+                  const float *bhi, const float *blo, int64_t ldb, int64_t m, int64_t n, const GemmParams &g,
+                  cudaStream_t st);
+
 constexpr int TC_K_ALIGN = 32;  // split-K ranges must be multiples of the 32-column TMA box
 
 }  // namespace gdr

@@ -234,10 +234,10 @@ int gdr_gss_loss_fwd_bwd_tc_f32(const float *embs, const int64_t *index, int64_t
   if ((rc = tc_gemm(EPI_GSS, ehi, elo, ehi, elo, b, b, d, d, d, d, 1, g, st))) return rc;   // G = E·Eᵀ -> loss, 2·dG
   loss_finalize_kernel<<<1, 256, 0, st>>>(partials, (int)(tiles * tiles), 1.0 / ((double)b * (double)b), loss_out);
   GDR_LAUNCHED();
-  if ((rc = tc_split(wm, ldw, ldw, nullptr, 0, 0, b, whi, wlo, st))) return rc;
+  (void)whi; (void)wlo;                                                                     // 2·dG is split in-kernel
   GemmParams q{};
   q.c = grad_e_out; q.ldc = d;
-  return tc_gemm(EPI_STORE, whi, wlo, ethi, etlo, b, d, ldw, ldw, ldw, ldw, 1, q, st);       // dE = 2·dG · E
+  return tc_gemm_raw_a(EPI_STORE, wm, ldw, ldw, nullptr, 0, 0, ethi, etlo, ldw, b, d, q, st);  // dE = 2·dG · E
 }
 
 int gdr_adam_step_multi_f32(int n_tensors, float *const *params, const float *const *grads, float *const *exp_avg,
