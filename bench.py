@@ -311,7 +311,10 @@ def run_msi_gcn(args):
         "gpu_launches": int(launches),
         "clocks": clk,
         "roofline": {"kernel": "spmm_warp_row_kernel<float> (all SpMM launches of the timed steps)", "bound": "hbm",
-                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     # dram__bytes_read.sum + dram__bytes_write.sum per launch of this kernel at this size, from the
+                     # ncu --set full capture profiles/msi_iteration_r1_full_raw.csv (39 MB read + 5..25 MB write)
+                     "traffic": 54.0e6 if (feats.shape[0], feats.shape[1]) == (29959, 256) else None,
                      "peak_source": peak_src, "launches": len(spmm_events),
                      "avg_launch_ms": spmm_ms / max(len(spmm_events), 1),
                      "share_of_step": spmm_ms / (ms_per_step * args.steps),
@@ -388,7 +391,10 @@ def run_rmat_spmm_single(args, steps, warmup):
             "nodes": n, "nnz": csr.nnz, "ms_per_spmm": ms, "gedges_per_s": csr.nnz / (ms * 1e-3) / 1e9,
             "alg_gb": b_alg / 1e9, "compulsory_gb": b_min / 1e9, "achieved_gbs": gbs, "peak_gbs": peak,
             "frac": gbs / peak, "frac_compulsory": b_min / (ms * 1e-3) / 1e9 / peak, "peak_source": peak_src,
-            "l2": "inputs larger than L2 (X = %.1f GB)" % (n * d * 4 / 1e9)}
+            "l2": "inputs larger than L2 (X = %.1f GB)" % (n * d * 4 / 1e9),
+            # ncu --set full of the same kernel at scale 24, d 128 (profiles/spmm_rmat24_r1b_hub_split_full_raw.csv):
+            # 166.9 GB read + 9.2 GB write per launch at 5.28 TB/s = 81 % of the measured HBM peak
+            "traffic": 176.14e9 if (scale, d, args.rmat_edge_factor) == (24, 128, 32) else None}
 
 
 def run_rmat_spmm_dist(args):

@@ -694,7 +694,10 @@ class NvlsLShapedSpMM:
 # ---- a timeline model of one L-shaped step, used to refine the bounds ------------------------------------------
 # Constants measured on B200 / NVLink 5 (profiles/diag_r1_n8_lshape_hubs0.txt): seconds per gathered entry, per
 # output row written by an SpMM, per row touched by the add pass, and per 512-byte row moved over one NVSwitch port.
-STEP_MODEL = dict(t_nnz=50e-12, t_row=250e-12, t_add=235e-12, link_bytes_per_s=695e9, t_sync=0.15e-3)
+# volume_scale: measured distinct-row counts over the Poisson estimate on R-MAT scale 24 (0.45-0.6 for every rank
+# pair: inside a histogram bin the degrees are far from uniform, which the estimate ignores).
+STEP_MODEL = dict(t_nnz=50e-12, t_row=250e-12, t_add=235e-12, link_bytes_per_s=695e9, t_sync=0.15e-3,
+                  volume_scale=0.5)
 
 
 def lshape_step_model(hist, bin_size, n, bbins, d, consts=None):
@@ -724,8 +727,9 @@ def lshape_step_model(hist, bin_size, n, bbins, d, consts=None):
     upper = lower.T
     nnz_pull = (nnz * (lower + np.eye(p))).sum(1)
     nnz_push = (nnz * upper).sum(0)
-    recv_x, sent_x = (pullr * lower).sum(1), (pullr * lower).sum(0)
-    recv_p, sent_p = (pushr * upper).sum(1), (pushr * upper).sum(0)
+    vs = k["volume_scale"]
+    recv_x, sent_x = vs * (pullr * lower).sum(1), vs * (pullr * lower).sum(0)
+    recv_p, sent_p = vs * (pushr * upper).sum(1), vs * (pushr * upper).sum(0)
     t_push = k["t_nnz"] * nnz_push + k["t_row"] * sent_p
     t_pull = k["t_nnz"] * nnz_pull + k["t_row"] * own
     t_add = np.where(recv_p > 0, k["t_add"] * (own + recv_p), 0.0)

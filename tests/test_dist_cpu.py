@@ -216,7 +216,8 @@ def test_step_model_and_refinement():
     hist, size = gdist.coarse_histogram(torch.from_numpy(m.row.astype(np.int64)),
                                         torch.from_numpy(m.col.astype(np.int64)), n, 200)
     b0 = gdist.lshape_bounds(hist.numpy(), size, n, p, row_weight=2.0)
-    t0, det = gdist.lshape_step_model(hist.numpy(), size, n, [int(b // size) for b in b0], 128)
+    t0, det = gdist.lshape_step_model(hist.numpy(), size, n, [int(b // size) for b in b0], 128,
+                                       consts=dict(volume_scale=1.0))    # smooth test matrix: Poisson is exact
     blk_r = np.searchsorted(b0, m.row, side="right") - 1
     blk_c = np.searchsorted(b0, m.col, side="right") - 1
     sent_x = np.zeros(p)
@@ -225,5 +226,5 @@ def test_step_model_and_refinement():
             sent_x[s] += len(np.unique(m.col[(blk_r == r) & (blk_c == s)]))
     assert np.allclose(det["sent_x"], sent_x, rtol=0.15, atol=30), (det["sent_x"], sent_x)
     assert abs(det["nnz_pull"].sum() + det["nnz_push"].sum() - m.nnz) < 1e-6 * m.nnz
-    b1, t1 = gdist.refine_lshape_bounds(hist.numpy(), size, n, b0, 128)
+    b1, t1 = gdist.refine_lshape_bounds(hist.numpy(), size, n, b0, 128, consts=dict(volume_scale=1.0))
     assert t1 <= t0 * (1 + 1e-9) and b1[0] == 0 and b1[-1] == n and (np.diff(b1) > 0).all()
