@@ -58,8 +58,9 @@ def parse_args():
     p.add_argument("--hubs", type=int, default=0,
                    help="N>1, lshape: the lowest K ranks exchange through NVSwitch multicast (multimem broadcast of "
                         "their X block, in-switch reduction of their partial rows)")
-    p.add_argument("--no-refine", action="store_true",
-                   help="N>1, lshape: keep the cost-cap bounds (skip the descent on the step timeline model)")
+    p.add_argument("--refine", action="store_true",
+                   help="N>1, lshape: descend on the step timeline model from the cost-cap bounds (measured: no gain "
+                        "at p = 8 on R-MAT 24, 7.5 vs 7.3 ms, so it is off by default)")
     p.add_argument("--comm-weight", type=float, default=0.0,
                    help="N>1, lshape: cost of one row moved, in nnz-equivalents, in the partition's balance")
     p.add_argument("--two-comms", action="store_true", help="N>1, lshape: partial rows on a second NCCL communicator")
@@ -422,7 +423,7 @@ def run_rmat_spmm_dist(args):
         hist_np = hist.cpu().numpy()
         bounds = gdist.lshape_bounds(hist_np, bin_size, n, world, row_weight=args.row_weight,
                                      comm_weight=args.comm_weight)
-        if not args.no_refine:
+        if args.refine:
             bounds, _pred = gdist.refine_lshape_bounds(hist_np, bin_size, n, bounds, d)
     else:
         rp = full.rowptr.cpu().numpy().astype(np.int64)
