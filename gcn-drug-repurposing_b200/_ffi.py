@@ -69,6 +69,10 @@ _SIGNATURES = {
     "gdr_gram_percentile_workspace_bytes": (c_i64, [c_i64, c_i64]),
     "gdr_gram_percentile_f32": (c_i32, [c_ptr, c_i64, c_i64, c_f64, ctypes.POINTER(c_f32), c_ptr, c_i64, c_ptr]),
     "gdr_gram_topk_f64": (c_i32, [c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr]),
+    "gdr_text_savetxt_bytes": (c_i64, [c_i64, c_i64]),
+    "gdr_text_savetxt_e18": (c_i64, [c_ptr, c_i64, c_i64, c_i32, ctypes.c_char_p, c_i64, c_i32]),
+    "gdr_text_parse_embs": (c_i64, [ctypes.c_char_p, c_i64, c_i32, c_ptr, c_i64, c_ptr, c_ptr,
+                                    ctypes.POINTER(c_i64), c_i32]),
     "gdr_mc_broadcast_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i32, c_ptr]),
     "gdr_mc_reduce_add_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i32, c_ptr]),
     "gdr_push_rows_f32": (c_i32, [c_ptr, c_i64, c_i32, c_ptr, c_ptr, c_ptr, c_ptr, c_i32, c_ptr]),

@@ -16,6 +16,7 @@ import torch
 
 from .dataset import DiffusionDataLoader, DiffusionDataSet
 from .optim import Adam
+from .textio import savetxt_e18
 from .helper import (combine_graph, convert_sparse_matrix_to_sparse_tensor, gen_graph, gram_percentile,
                      preprocess_graph)
 from .model import GSS_loss, ResidualGraphConvolutionalNetwork
@@ -138,7 +139,8 @@ def main(args):
         train_time = time.time() - start_time  # noqa: F841  (computed and unused upstream as well)
         itr += 1
         print(f"iter {itr}")
-    np.savetxt(args.out_file, trainer.hidden_emb.cpu().data)
+    # train.py:193 np.savetxt(..., hidden_emb): same bytes, rows formatted in parallel by libgdr's host code
+    savetxt_e18(args.out_file, trainer.hidden_emb.detach().cpu().numpy())
     return trainer
 
 

@@ -265,6 +265,18 @@ int gdr_rwr_solve_f64(const int32_t *m_rowptr, const int32_t *m_col, const doubl
                       int64_t max_iter, double *x_out, int32_t *iters_out, void *workspace,
                       int64_t workspace_bytes, gdr_stream_t stream);
 
+/* ---- host-side text formats around the path (no device work) ------------------------------------------ *
+ * graph_embs.txt exactly as np.savetxt(fname, hidden_emb) writes it (train.py:193; '%.18e', ' ', '\n', no header):
+ * returns the bytes written or a negative GDR_E_* code.  x is a HOST array [n, d] of fp32 (4) or fp64 (8).      */
+int64_t gdr_text_savetxt_bytes(int64_t n, int64_t d);
+int64_t gdr_text_savetxt_e18(const void *x, int64_t n, int64_t d, int elem_bytes, char *out, int64_t out_cap,
+                             int n_threads);
+/* node2vec .embs.txt as train.py:79-80 consumes it (skip_rows header lines; first column = node name, the rest
+ * float()).  values == NULL: returns the number of data lines, *d_out = value columns.  Otherwise fills
+ * values[N, d] (fp64) and the byte span of every name; returns N or a negative code.                           */
+int64_t gdr_text_parse_embs(const char *text, int64_t len, int skip_rows, double *values, int64_t d,
+                            int64_t *name_off, int32_t *name_len, int64_t *d_out, int n_threads);
+
 #ifdef __cplusplus
 }
 #endif
