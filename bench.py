@@ -10,9 +10,12 @@ Workloads (BASELINE.json `metric`: "GCN epochs/s on MSI graph; SpMM GEdges/s + H
              train.sh hyper-parameters.  One step = one epoch = ceil(N/B) = 15 iterations of
              (full-graph forward + batch GSS loss + backward + Adam), train.py:155-184.  metric = epochs/s.
              The same line carries `spmm_rmat`: the HBM-bound SpMM number on an R-MAT graph at 1 GPU.
-  rmat_spmm  (default at N>1; BASELINE configs[4]) SpMM Y = Â·X on an R-MAT graph, d=128, rows partitioned by
-             nnz over the ranks, NCCL all-gather of the feature blocks.  One step = one SpMM over the whole
-             graph.  metric = GEdges/s (strong scaling).
+  rmat_spmm  (default at N>1; BASELINE configs[4]) SpMM Y = Â·X on an R-MAT graph (scale 24, edge factor 32,
+             d=128), L-shaped partition over the ranks (gcn-drug-repurposing_b200/dist.py): only the referenced
+             X rows / the partial Y rows travel, as direct stores into peer symmetric memory over NVLink
+             (--transport nccl: all_to_all of packed rows; --hubs K: NVSwitch multicast for the hub ranks;
+             --partition rows: plain row blocks).  One step = one SpMM over the whole graph, exchanges included.
+             metric = GEdges/s (strong scaling); the line carries the same product's 1-GPU time.
 
 One JSON line on stdout (rank 0).  See DESIGN.md §Measurement for every field.
 """

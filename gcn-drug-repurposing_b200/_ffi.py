@@ -64,6 +64,9 @@ _SIGNATURES = {
                                             c_i64, c_ptr]),
     "gdr_gram_percentile_tc_workspace_bytes": (c_i64, [c_i64, c_i64]),
     "gdr_gram_percentile_tc_f32": (c_i32, [c_ptr, c_i64, c_i64, c_f64, ctypes.POINTER(c_f32), c_ptr, c_i64, c_ptr]),
+    "gdr_linear_bwd_weight2_tc_workspace_bytes": (c_i64, [c_i64, c_i64]),
+    "gdr_linear_bwd_weight2_tc_f32": (c_i32, [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_i32, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr,
+                                              c_i64, c_ptr]),
     "gdr_gather_rows_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr]),
     "gdr_scatter_rows_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr]),
     "gdr_gram_percentile_workspace_bytes": (c_i64, [c_i64, c_i64]),

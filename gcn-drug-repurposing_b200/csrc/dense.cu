@@ -104,6 +104,34 @@ splitk_reduce_kernel(const float *__restrict__ part, int splits, int64_t count, 
   }
 }
 
+// the same for partials of a [d, 2d] product whose left / right halves are two separate [d, d] outputs (dW1 | dW2);
+// out2 == nullptr: only the left half exists (width d).  `dup` != 0: out2 receives the SAME sum as out1 (db1 = db2).
+__global__ void __launch_bounds__(256)
+splitk_reduce2_kernel(const float *__restrict__ part, int splits, int64_t rows, int64_t d, int accumulate, int dup,
+                      float *__restrict__ out1, float *__restrict__ out2) {
+  __shared__ float red[8][32];
+  const int o = threadIdx.x & 31, zl = threadIdx.x >> 5;
+  const int64_t width = dup ? d : 2 * d;
+  const int64_t count = rows * width;
+  const int64_t i = (int64_t)blockIdx.x * 32 + o;
+  float s = 0.f;
+  if (i < count)
+    for (int z = zl; z < splits; z += 8) s += part[(int64_t)z * count + i];
+  red[zl][o] = s;
+  __syncthreads();
+  if (zl == 0 && i < count) {
+    const float t = ((red[0][o] + red[1][o]) + (red[2][o] + red[3][o])) + ((red[4][o] + red[5][o]) + (red[6][o] + red[7][o]));
+    if (dup) {
+      out1[i] = accumulate ? out1[i] + t : t;
+      out2[i] = accumulate ? out2[i] + t : t;
+    } else {
+      const int64_t m = i / width, j = i - m * width;
+      float *dst = j < d ? out1 + m * d + j : out2 + m * d + (j - d);
+      *dst = accumulate ? *dst + t : t;
+    }
+  }
+}
+
 // column sums of G[n,d] -> partial[blocks][d]; each block owns a slab of CS_ROWS rows.  256 threads =
 // 64 float4 column groups x 4 row lanes (4 rows in flight per column group), fixed-order combine in
 // shared memory: deterministic.
@@ -377,6 +405,69 @@ int gdr_linear_bwd_weight_tc_f32(const float *g, const float *a, int64_t n, int6
                                                                              db);
     GDR_LAUNCHED();
   }
+  return GDR_OK;
+}
+
+// Both weight gradients of a layer from ONE split-K product: [dW1 | dW2] = Gᵀ·[A1 | A2] (G is transposed and split
+// once, N = 2d gives twice the tiles per K range), and db1 = db2 = colsum(G) from one pass (Z = Z1 + Z2, so both
+// biases see the same gradient).  modules/model.py:165,170 under autograd.
+int64_t gdr_linear_bwd_weight2_tc_workspace_bytes(int64_t n, int64_t d) {
+  if (n < 0 || d <= 0) return GDR_E_BADARG;
+  const int64_t tiles = ceil_div<int64_t>(d, 128) * ceil_div<int64_t>(2 * d, 128);
+  int64_t s = ceil_div<int64_t>(2 * kNumSMs, tiles);
+  int64_t per = align_up(ceil_div<int64_t>(n > 0 ? n : 1, s), TC_K_ALIGN);
+  if (per < 4 * TC_K_ALIGN) per = 4 * TC_K_ALIGN;
+  const int64_t splits = ceil_div<int64_t>(n > 0 ? n : 1, per);
+  const int64_t ldt = align_up(n > 0 ? n : 1, 4);
+  const int64_t cs_blocks = ceil_div<int64_t>(n > 0 ? n : 1, CS_ROWS);
+  return 2 * align_up(d * ldt * 4, 256) + 2 * align_up(2 * d * ldt * 4, 256) + align_up(splits * d * 2 * d * 4, 256) +
+         align_up(cs_blocks * d * 4, 256) + 1024;
+}
+
+int gdr_linear_bwd_weight2_tc_f32(const float *g, const float *a1, const float *a2, int64_t n, int64_t d,
+                                  int accumulate, float *dw1, float *db1, float *dw2, float *db2, void *workspace,
+                                  int64_t workspace_bytes, gdr_stream_t stream) {
+  GDR_CHECK_ARG(n >= 0 && d > 0 && g && a1 && a2 && dw1 && dw2 && db1 && db2 && workspace, GDR_E_BADARG,
+                "linear_bwd_weight2_tc: bad args");
+  GDR_CHECK_ARG(d % 4 == 0, GDR_E_SHAPE, "linear_bwd_weight2_tc: d must be a multiple of 4");
+  GDR_CHECK_ARG(workspace_bytes >= gdr_linear_bwd_weight2_tc_workspace_bytes(n, d), GDR_E_WORKSPACE,
+                "linear_bwd_weight2_tc: workspace too small");
+  cudaStream_t st = as_stream(stream);
+  if (n == 0) {
+    if (!accumulate) {
+      GDR_CUDA(cudaMemsetAsync(dw1, 0, d * d * 4, st));
+      GDR_CUDA(cudaMemsetAsync(dw2, 0, d * d * 4, st));
+      GDR_CUDA(cudaMemsetAsync(db1, 0, d * 4, st));
+      GDR_CUDA(cudaMemsetAsync(db2, 0, d * 4, st));
+    }
+    return GDR_OK;
+  }
+  const int64_t tiles = ceil_div<int64_t>(d, 128) * ceil_div<int64_t>(2 * d, 128);
+  int64_t per = align_up(ceil_div<int64_t>(n, ceil_div<int64_t>(2 * kNumSMs, tiles)), TC_K_ALIGN);
+  if (per < 4 * TC_K_ALIGN) per = 4 * TC_K_ALIGN;
+  const int splits = (int)ceil_div<int64_t>(n, per);
+  const int64_t ldt = align_up(n, 4);
+  const int64_t cs_blocks = ceil_div<int64_t>(n, CS_ROWS);
+  Carver cv(workspace);
+  float *ghi = cv.take<float>(d * ldt), *glo = cv.take<float>(d * ldt);
+  float *ahi = cv.take<float>(2 * d * ldt), *alo = cv.take<float>(2 * d * ldt);
+  float *part = cv.take<float>((int64_t)splits * d * 2 * d);
+  float *cpart = cv.take<float>(cs_blocks * d);
+  int rc;
+  if ((rc = tc_split_transpose(g, d, n, d, ldt, ghi, glo, st))) return rc;                         // A(m=out, k=node)
+  if ((rc = tc_split_transpose(a1, d, n, d, ldt, ahi, alo, st))) return rc;                        // B rows 0..d-1
+  if ((rc = tc_split_transpose(a2, d, n, d, ldt, ahi + d * ldt, alo + d * ldt, st))) return rc;    // B rows d..2d-1
+  GemmParams q{};
+  q.c = part; q.ldc = 2 * d;
+  if ((rc = tc_gemm(EPI_SPLITK, ghi, glo, ahi, alo, d, 2 * d, n, ldt, ldt, per, splits, q, st))) return rc;
+  splitk_reduce2_kernel<<<(unsigned)ceil_div<int64_t>(d * 2 * d, 32), 256, 0, st>>>(part, splits, d, d, accumulate, 0,
+                                                                                 dw1, dw2);
+  GDR_LAUNCHED();
+  colsum_partial_kernel<<<(unsigned)cs_blocks, 256, 0, st>>>(g, n, d, cpart);
+  GDR_LAUNCHED();
+  splitk_reduce2_kernel<<<(unsigned)ceil_div<int64_t>(d, 32), 256, 0, st>>>(cpart, (int)cs_blocks, 1, d, accumulate, 1,
+                                                                         db1, db2);
+  GDR_LAUNCHED();
   return GDR_OK;
 }
 

@@ -19,6 +19,12 @@ then accumulates in place (gdr_spmm_csr_f32 with e1 = y).  Results are determini
 
 The reference has no distributed code at all; this module is new surface, kept to the one
 exchange step the path really has.
+
+Classes, in the order they were measured (DESIGN.md §4 has the numbers):
+    RowPartitionedSpMM   the design above (pull only, NCCL all-to-all)
+    LShapedSpMM          blocks above the diagonal are multiplied at the column owner and their partial rows
+                         sent back; transport "nccl" or "p2p" (gdr_push_rows_f32 into peer symmetric memory)
+    NvlsLShapedSpMM      the same with NVSwitch multicast / in-switch reduction for the hub ranks
 """
 import numpy as np
 import torch

@@ -71,11 +71,10 @@ def layer_backward_raw(csr_t, gz, x, p, t, w1, w2, grads, accumulate, need_gx, w
     dw1, db1, dw2, db2 = grads
     acc = 1 if accumulate else 0
     if GEMM_BACKEND == "tc":
-        wsw = _ffi.workspace(L.gdr_linear_bwd_weight_tc_workspace_bytes(n, d), x.device)
-        _ffi.check(L.gdr_linear_bwd_weight_tc_f32(_ffi.ptr(gz), _ffi.ptr(p), n, d, acc, _ffi.ptr(dw1), _ffi.ptr(db1),
-                                                  _ffi.ptr(wsw), wsw.numel(), _ffi.stream()), "linear_bwd_weight_tc(W1)")
-        _ffi.check(L.gdr_linear_bwd_weight_tc_f32(_ffi.ptr(gz), _ffi.ptr(t), n, d, acc, _ffi.ptr(dw2), _ffi.ptr(db2),
-                                                  _ffi.ptr(wsw), wsw.numel(), _ffi.stream()), "linear_bwd_weight_tc(W2)")
+        wsw = _ffi.workspace(L.gdr_linear_bwd_weight2_tc_workspace_bytes(n, d), x.device)
+        _ffi.check(L.gdr_linear_bwd_weight2_tc_f32(_ffi.ptr(gz), _ffi.ptr(p), _ffi.ptr(t), n, d, acc, _ffi.ptr(dw1),
+                                                   _ffi.ptr(db1), _ffi.ptr(dw2), _ffi.ptr(db2), _ffi.ptr(wsw),
+                                                   wsw.numel(), _ffi.stream()), "linear_bwd_weight2_tc")
         if not need_gx:
             return None
         wsi = _ffi.workspace(L.gdr_linear_bwd_input_tc_workspace_bytes(n, d), x.device)

@@ -176,6 +176,11 @@ int gdr_linear_bwd_weight_tc_f32(const float *g, const float *a, int64_t n, int6
                                  float *dw, float *db, void *workspace, int64_t workspace_bytes,
                                  gdr_stream_t stream);
 
+/* Both weight gradients of a layer from one split-K product [dW1 | dW2] = Gᵀ·[A1 | A2], db1 = db2 = colsum(G). */
+int64_t gdr_linear_bwd_weight2_tc_workspace_bytes(int64_t n, int64_t d);
+int gdr_linear_bwd_weight2_tc_f32(const float *g, const float *a1, const float *a2, int64_t n, int64_t d,
+                                  int accumulate, float *dw1, float *db1, float *dw2, float *db2,
+                                  void *workspace, int64_t workspace_bytes, gdr_stream_t stream);
 int64_t gdr_gss_loss_tc_workspace_bytes(int64_t b, int64_t d);
 int gdr_gss_loss_fwd_bwd_tc_f32(const float *embs, const int64_t *index, int64_t b, int64_t n, int64_t d,
                                 float alpha, float beta, float *loss_out, float *grad_e_out,
