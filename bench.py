@@ -446,14 +446,18 @@ def run_rmat_spmm_dist(args):
     ms_1gpu = t1a.elapsed_time(t1b) / 3
     del y_full
     if args.partition == "lshape":
+        transport = args.transport
+        if transport == "p2p" and not gdist.p2p_available(dev):
+            transport = "nccl"                      # no peer mapping on this box: NCCL all-to-all, two communicators
+            args.two_comms, args.hubs = True, 0
         g2 = dist.new_group(backend="nccl", pg_options=dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)) \
-            if args.two_comms else None
+            if (args.two_comms and transport == "nccl") else None
         if args.hubs > 0:
             part = gdist.NvlsLShapedSpMM.from_full(full, bounds, rank, world, d, n_hubs=args.hubs,
                                                    push_ctas=args.push_ctas)
         else:
             part = gdist.LShapedSpMM.from_full(full, bounds, rank, world, d, group_partials=g2,
-                                               transport=args.transport, push_ctas=args.push_ctas)
+                                               transport=transport, push_ctas=args.push_ctas)
     else:
         part = gdist.RowPartitionedSpMM.from_full(full, bounds, rank, world, d, overlap=not args.no_overlap)
     del full
@@ -579,7 +583,8 @@ def run_rmat_spmm_dist(args):
                     "steps": e2e_steps, "h2d_bytes_per_step": int(io[0].item()), "d2h_bytes_per_step": int(io[1].item()),
                     "note": "every rank uploads its X block from pinned host memory and downloads its Y block, each step"},
             "gpu_launches": int(launches.item()), "clocks": clk,
-            "roofline": {"kernel": "spmm_warp_row_kernel<float> + all-gather", "bound": "hbm",
+            "roofline": {"kernel": "spmm_warp_row_kernel<float> (push + pull + add products of every rank) with the exchange "
+                                   "(push_rows_kernel / NCCL) inside the step", "bound": "hbm",
                          "achieved": gbs, "peak": peak * world, "unit": "GB/s", "frac": gbs / (peak * world),
                          "traffic": None, "peak_source": peak_src + f" x{world} GPUs",
                          "exchange_bytes_in_rank0": int(part.recv_rows * d * 4),

@@ -73,6 +73,23 @@ def split_csr(rowptr, new_col, val, keep, n_rows, n_cols):
                      n_rows, n_cols)
 
 
+def p2p_available(device, group=None):
+    """True on every rank iff a symmetric-memory rendezvous (peer pointers over NVLink) comes up on all of them.
+    Collective.  Used to choose between the two CUDA transports of LShapedSpMM ("p2p" stores vs NCCL all-to-all);
+    it never selects a CPU path."""
+    ok = 1
+    try:
+        import torch.distributed._symmetric_memory as symm
+        t = symm.empty(1024, dtype=torch.float32, device=device)
+        h = symm.rendezvous(t, (group or dist.group.WORLD).group_name)
+        ok = 1 if len(h.buffer_ptrs) == dist.get_world_size(group) and all(int(p) != 0 for p in h.buffer_ptrs) else 0
+    except Exception:  # noqa: BLE001  (any failure means "use the NCCL transport")
+        ok = 0
+    flag = torch.tensor([ok], dtype=torch.int32, device=device)
+    dist.all_reduce(flag, op=dist.ReduceOp.MIN, group=group)
+    return bool(flag.item())
+
+
 class RowPartitionedSpMM:
     """This rank's row block of Â plus the buffers and index lists of the exchange step."""
 
