@@ -602,6 +602,9 @@ def run_reference(args, workload):
     modules/model.py + train.py call them; restated in oracle/gcn_oracle.py because /root/reference does not
     travel to the GPU box), all host threads.  Each step is a bounded sample of the workload."""
     import torch
+    # torchrun exports OMP_NUM_THREADS=1; the reference arm is the only work on the box while it runs (the other
+    # ranks exit at once), so it gets every host thread
+    torch.set_num_threads(max(1, os.cpu_count() or 1))
     cores = torch.get_num_threads()
     if workload == "msi_gcn":
         a, feats = msi_inputs()
