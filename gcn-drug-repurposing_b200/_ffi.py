@@ -85,6 +85,14 @@ _SIGNATURES = {
     "gdr_rwr_workspace_bytes": (c_i64, [c_i64, c_i64, c_i64]),
     "gdr_rwr_solve_f64": (c_i32, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_i64,
                                   c_f64, c_f64, c_i64, c_ptr, c_ptr, c_ptr, c_i64, c_ptr]),
+    "gdr_rwr_refine_f64": (c_i32, [c_ptr, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr]),
+    "gdr_rwr_power_iteration_workspace_bytes": (c_i64, [c_i64]),
+    "gdr_rwr_power_iteration_f64": (c_i32, [c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_f64, c_f64, c_i64, c_ptr,
+                                            ctypes.POINTER(c_i32), c_ptr, c_i64, c_ptr]),
+    "gdr_rank_workspace_bytes": (c_i64, [c_i64]),
+    "gdr_rank_embedding_f64": (c_i32, [c_ptr, c_i64, c_i64, c_i32, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr,
+                                       c_i64, c_ptr]),
+    "gdr_rank_values_f64": (c_i32, [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_ptr]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

@@ -49,7 +49,7 @@ __device__ double rw_pairwise(const double *__restrict__ val, const int32_t *__r
   off[0] = 0, len[0] = n, st[0] = 0;
   auto at = [&](int i) -> double {
     const int32_t e = base + i;
-    return rw_keep(flag[e], u, col[e], seed) ? val[e] : 0.0;
+    return (flag == nullptr || rw_keep(flag[e], u, col[e], seed)) ? val[e] : 0.0;
   };
   while (sp >= 0) {
     const int o = off[sp], l = len[sp];
@@ -225,6 +225,96 @@ __global__ void rw_iota_kernel(int32_t *p, int64_t n) {
   if (i < n) p[i] = (int32_t)i;
 }
 
+// =============================================================================================
+// Per-seed API of the reference (DiffusionProfiles.refine_M_S / power_iteration called with a
+// caller-supplied matrix): one vector, same accumulation orders as above.
+// =============================================================================================
+
+// refine_M_S (:49-56): S[u] = 1/rowsum(u) (numpy reduceat order; 0 stays 0) and val_out = S[row]*val
+// (scipy's Q*M: one product per entry).
+__global__ void __launch_bounds__(128)
+rw1_refine_kernel(const int32_t *__restrict__ rowptr, const int32_t *__restrict__ col,
+                  const double *__restrict__ val, int64_t n, double *__restrict__ S, double *__restrict__ val_out) {
+  const int64_t u = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= n) return;
+  const int32_t b = rowptr[u], e = rowptr[u + 1];
+  double sum = 0.0;
+  if (e > b) {
+    const double first = val[b];
+    sum = (e - b > 1) ? __dadd_rn(first, rw_pairwise(val, col, nullptr, b + 1, e - b - 1, (int32_t)u, -1)) : first;
+  }
+  const double sc = sum != 0.0 ? 1.0 / sum : 0.0;
+  S[u] = sc;
+  for (int32_t j = b; j < e; ++j) val_out[j] = __dmul_rn(sc, val[j]);
+}
+
+// p <- p / p.sum()  (numpy pairwise sum, one thread) ; x <- 1/N ; dangling list = ascending u with S[u] == 0
+__global__ void rw1_prepare_kernel(double *__restrict__ p, const double *__restrict__ S, int64_t n,
+                                   double *__restrict__ x, int32_t *__restrict__ dang, int32_t *__restrict__ n_dang) {
+  __shared__ double total;
+  if (threadIdx.x == 0) {
+    total = rw_pairwise(p, nullptr, nullptr, 0, (int)n, 0, -1);
+    int c = 0;
+    for (int64_t u = 0; u < n; ++u)
+      if (S[u] == 0.0) dang[c++] = (int32_t)u;
+    *n_dang = c;
+  }
+  __syncthreads();
+  const double t = total, x0 = 1.0 / (double)n;
+  for (int64_t i = threadIdx.x; i < n; i += blockDim.x) {
+    p[i] = p[i] / t;
+    x[i] = x0;
+  }
+}
+
+// Python's sum(x[is_dangling]): sequential over ascending dangling nodes
+__global__ void rw1_dangling_kernel(const double *__restrict__ x, const int32_t *__restrict__ dang,
+                                    const int32_t *__restrict__ n_dang, double *__restrict__ dsum) {
+  double acc = 0.0;
+  const int c = *n_dang;
+  for (int i = 0; i < c; ++i) acc = __dadd_rn(acc, x[dang[i]]);
+  *dsum = acc;
+}
+
+// x_new = alpha*(x*M + dsum*p) + (1-alpha)*p with x*M as scipy's csc_matvec on M.T: sources ascending,
+// separate multiply and add.  Mt = CSR of the transpose of the (already row-scaled) M.
+__global__ void __launch_bounds__(128)
+rw1_step_kernel(const int32_t *__restrict__ t_rowptr, const int32_t *__restrict__ t_col,
+                const double *__restrict__ t_val, int64_t n, const double *__restrict__ x,
+                const double *__restrict__ p, const double *__restrict__ dsum, double alpha, double oma,
+                double *__restrict__ x_new, double *__restrict__ err_part) {
+  __shared__ double red[4];
+  const int64_t v = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  double err = 0.0;
+  if (v < n) {
+    double acc = 0.0;
+    for (int32_t j = t_rowptr[v]; j < t_rowptr[v + 1]; ++j) acc = __dadd_rn(acc, __dmul_rn(t_val[j], x[t_col[j]]));
+    const double pv = p[v];
+    const double t = __dadd_rn(acc, __dmul_rn(*dsum, pv));
+    const double xn = __dadd_rn(__dmul_rn(alpha, t), __dmul_rn(oma, pv));
+    x_new[v] = xn;
+    err = fabs(xn - x[v]);
+  }
+  err = warp_sum(err);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = err;
+  __syncthreads();
+  if (threadIdx.x == 0) err_part[blockIdx.x] = (red[0] + red[1]) + (red[2] + red[3]);
+}
+
+__global__ void rw1_err_kernel(const double *__restrict__ err_part, int n_blocks, double *__restrict__ err_out) {
+  __shared__ double red[32];
+  double s = 0.0;
+  for (int i = threadIdx.x; i < n_blocks; i += blockDim.x) s += err_part[i];
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double t = 0.0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) t += red[w];
+    *err_out = t;
+  }
+}
+
 struct RwPlan {
   int64_t sp, n_tiles;
   size_t select_tmp;
@@ -331,6 +421,79 @@ int gdr_rwr_solve_f64(const int32_t *m_rowptr, const int32_t *m_col, const doubl
   if (n_done < n_seeds) {
     set_error("rwr_solve: power iteration failed to converge in %lld iterations for %lld of %lld seeds",
               (long long)max_iter, (long long)(n_seeds - n_done), (long long)n_seeds);
+    return GDR_E_NOCONV;
+  }
+  return GDR_OK;
+}
+
+// refine_M_S (diffusion_profiles.py:49-56) for a caller-supplied matrix: s_out[n] = 1/rowsum (0 stays 0),
+// val_out[nnz] = s_out[row] * val.  The host mirror rebuilds scipy's Q*M structure from it.
+int gdr_rwr_refine_f64(const int32_t *rowptr, const int32_t *col, const double *val, int64_t n, int64_t nnz,
+                       double *s_out, double *val_out, gdr_stream_t stream) {
+  GDR_CHECK_ARG(n > 0 && nnz >= 0 && rowptr && s_out, GDR_E_BADARG, "rwr_refine: bad args");
+  GDR_CHECK_ARG(nnz == 0 || (col && val && val_out), GDR_E_BADARG, "rwr_refine: null matrix arrays");
+  rw1_refine_kernel<<<(unsigned)ceil_div<int64_t>(n, 128), 128, 0, as_stream(stream)>>>(rowptr, col, val, n, s_out,
+                                                                                      val_out);
+  GDR_LAUNCHED();
+  return GDR_OK;
+}
+
+int64_t gdr_rwr_power_iteration_workspace_bytes(int64_t n) {
+  if (n < 0) return GDR_E_BADARG;
+  const int64_t blocks = ceil_div<int64_t>(n > 0 ? n : 1, 128);
+  return 3 * align_up(n * 8, 256) + align_up(blocks * 8, 256) + align_up((n + 1) * 4, 256) + 1024;
+}
+
+// power_iteration(M, S, nodelist, per_dict) (diffusion_profiles.py:65-90) for ONE personalisation vector and a
+// caller-supplied, already row-scaled M (given as the CSR of its transpose, sources ascending).  s[n]: the S of
+// refine_M_S (only S == 0, the dangling rows, matters); p[n]: per_dict values in nodelist order (normalised
+// here, p / p.sum()).  x_out[n]; *iters_out_host = iterations used.  Synchronises the stream every iteration
+// (the L1 stop test).  GDR_E_NOCONV after max_iter iterations (the reference raises).
+int gdr_rwr_power_iteration_f64(const int32_t *mt_rowptr, const int32_t *mt_col, const double *mt_val, int64_t n,
+                                const double *s, const double *p, double alpha, double tol, int64_t max_iter,
+                                double *x_out, int32_t *iters_out_host, void *workspace, int64_t workspace_bytes,
+                                gdr_stream_t stream) {
+  GDR_CHECK_ARG(n > 0 && max_iter >= 0 && mt_rowptr && s && p && x_out && workspace, GDR_E_BADARG,
+                "rwr_power_iteration: bad args");
+  GDR_CHECK_ARG(n < (int64_t)INT32_MAX, GDR_E_SHAPE, "rwr_power_iteration: int32 node range exceeded");
+  GDR_CHECK_ARG(workspace_bytes >= gdr_rwr_power_iteration_workspace_bytes(n), GDR_E_WORKSPACE,
+                "rwr_power_iteration: workspace too small");
+  cudaStream_t st = as_stream(stream);
+  const int blocks = (int)ceil_div<int64_t>(n, 128);
+  Carver cv(workspace);
+  double *pn = cv.take<double>(n), *xa = cv.take<double>(n), *xb = cv.take<double>(n);
+  double *err_part = cv.take<double>(blocks);
+  int32_t *dang = cv.take<int32_t>(n + 1);
+  double *scal = cv.take<double>(2);        // [0] dangling mass, [1] L1 error
+  int32_t *n_dang = cv.take<int32_t>(1);
+  GDR_CUDA(cudaMemcpyAsync(pn, p, n * 8, cudaMemcpyDeviceToDevice, st));
+  rw1_prepare_kernel<<<1, 1024, 0, st>>>(pn, s, n, xa, dang, n_dang);
+  GDR_LAUNCHED();
+  const double thresh = (double)n * tol, oma = 1.0 - alpha;
+  double *cur = xa, *nxt = xb;
+  int64_t it = 0;
+  bool converged = false;
+  while (!converged && it < max_iter) {
+    ++it;
+    rw1_dangling_kernel<<<1, 1, 0, st>>>(cur, dang, n_dang, scal);
+    GDR_LAUNCHED();
+    rw1_step_kernel<<<blocks, 128, 0, st>>>(mt_rowptr, mt_col, mt_val, n, cur, pn, scal, alpha, oma, nxt, err_part);
+    GDR_LAUNCHED();
+    rw1_err_kernel<<<1, 1024, 0, st>>>(err_part, blocks, scal + 1);
+    GDR_LAUNCHED();
+    double err = 0.0;
+    GDR_CUDA(cudaMemcpyAsync(&err, scal + 1, 8, cudaMemcpyDeviceToHost, st));
+    GDR_CUDA(cudaStreamSynchronize(st));
+    converged = err < thresh;
+    double *t = cur;
+    cur = nxt;
+    nxt = t;
+  }
+  GDR_CUDA(cudaMemcpyAsync(x_out, cur, n * 8, cudaMemcpyDeviceToDevice, st));
+  GDR_CUDA(cudaStreamSynchronize(st));
+  if (iters_out_host) *iters_out_host = (int32_t)it;
+  if (!converged) {
+    set_error("pagerank_scipy: power iteration failed to converge in %lld iterations.", (long long)max_iter);
     return GDR_E_NOCONV;
   }
   return GDR_OK;

@@ -57,6 +57,12 @@ template <typename T>
 __device__ __forceinline__ typename VecOf<T>::type vload(const T *p) {
   return __ldg(reinterpret_cast<const typename VecOf<T>::type *>(p));
 }
+// coherent 128-bit load: for operands that may alias the output (e1 == y, in-place accumulation) the
+// read-only (ld.global.nc) path is not defined
+template <typename T>
+__device__ __forceinline__ typename VecOf<T>::type vload_coherent(const T *p) {
+  return *reinterpret_cast<const typename VecOf<T>::type *>(p);
+}
 
 // acc += sum_{e in [s,e)} val[e] * x[col[e], :] (* mul[col[e], :]).  The warp fetches 32 (col,val) pairs
 // at a time, broadcasts them with shuffles and keeps 4 gathered rows (4*V 128-bit loads per lane) in flight.
@@ -198,7 +204,7 @@ spmm_warp_row_kernel(const int32_t *__restrict__ rowptr, const int32_t *__restri
 #pragma unroll
   for (int v = 0; v < V; ++v) {
     if (ADD) {
-      Vec a = vload<T>(e1 + row * D + loff + v * SLAB);
+      Vec a = vload_coherent<T>(e1 + row * D + loff + v * SLAB);  // e1 may be y itself
       if (e2 != nullptr) a = vmul(a, vload<T>(e2 + row * D + loff + v * SLAB));
       vadd(acc[v], a);
     }
@@ -216,8 +222,8 @@ template <typename T, bool MUL, bool ADD>
 __global__ void __launch_bounds__(256)
 spmm_warp_row_generic_kernel(const int32_t *__restrict__ rowptr, const int32_t *__restrict__ col,
                              const T *__restrict__ val, int64_t n_rows, int64_t d, const T *__restrict__ x,
-                             const T *__restrict__ mul, const T *__restrict__ e1, const T *__restrict__ e2,
-                             T *__restrict__ y, const T *__restrict__ m2, T *__restrict__ y2) {
+                             const T *__restrict__ mul, const T *e1, const T *__restrict__ e2,
+                             T *y, const T *__restrict__ m2, T *__restrict__ y2) {
   using Vec = typename VecOf<T>::type;
   constexpr int EPL = VecOf<T>::N;
   constexpr int SLAB = 32 * EPL;
@@ -251,7 +257,7 @@ spmm_warp_row_generic_kernel(const int32_t *__restrict__ rowptr, const int32_t *
     }
     if (live) {
       if (ADD) {
-        Vec a = vload<T>(e1 + row * d + cc);
+        Vec a = vload_coherent<T>(e1 + row * d + cc);  // e1 may be y itself
         if (e2 != nullptr) a = vmul(a, vload<T>(e2 + row * d + cc));
         vadd(acc, a);
       }

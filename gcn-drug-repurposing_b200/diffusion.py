@@ -1,6 +1,7 @@
 """Drop-in mirror of multiscale/diff_prof/diffusion_profiles.py:12-169 (class DiffusionProfiles).
 
-Same constructor, same public methods, same on-disk artefacts (`<clean(seed)>_p_visit_array.npy`
+Same constructor, same public methods (the per-seed ones included: convert_M_to_make_all_drugs_indications_sinks_
+except_selected, refine_M_S, power_iteration, with the reference's signatures and return types), same on-disk artefacts (`<clean(seed)>_p_visit_array.npy`
 fp64[N] in msi.nodelist order, plus whatever msi.save_graph / save_node2idx write), but all seeds are
 solved at once on the GPU by gdr_rwr_solve_f64 (csrc/rwr.cu): the per-seed matrix surgery
 (:29-47), the row normalisation (:49-56) and the power iteration (:65-90) run as one batched,
@@ -45,6 +46,23 @@ def sink_edge_flags(m, sink_pairs):
         hit = keys[pos] == want
         flag[pos[hit]] |= bit
     return flag
+
+
+def scaled_matrix_like_scipy(m, scaled_values):
+    """The csr_matrix scipy's `Q * M` (Q diagonal) returns, given M (sorted rows) and the products S[row]*M.data:
+    zero products dropped, every row's entries in reverse stored order (csr_matmat emits its per-row linked list
+    back to front), indices therefore unsorted.  Structure only; the products come from the device."""
+    n = m.shape[0]
+    v = np.asarray(scaled_values)
+    keep = v != 0.0
+    rows = np.repeat(np.arange(n, dtype=np.int64), np.diff(m.indptr))[keep]
+    cols_r, vals_r, rows_r = m.indices[keep][::-1], v[keep][::-1], rows[::-1]
+    order = np.argsort(rows_r, kind="stable")          # by row; inside a row the reversed order survives
+    indptr = np.zeros(n + 1, dtype=m.indptr.dtype)
+    np.cumsum(np.bincount(rows, minlength=n), out=indptr[1:])
+    out = sp.csr_matrix((vals_r[order], cols_r[order].astype(m.indices.dtype), indptr), shape=m.shape)
+    out.has_sorted_indices = False
+    return out
 
 
 class RwrProblem:
@@ -134,6 +152,76 @@ class DiffusionProfiles():
         return x.cpu().numpy(), it.cpu().numpy()
 
     # ---- per-seed API of the reference ------------------------------------------------------------
+    def convert_M_to_make_all_drugs_indications_sinks_except_selected(self, msi, selected_drugs_and_indications):
+        """:29-47 — a copy of `initial_M` (structure kept, explicit zeros stored) with the entries protein -> selected
+        and every out-edge (t, p), p in drug_or_indication2proteins[t], of every non-selected drug / indication t
+        zeroed.  Index surgery only (no arithmetic): positions come from the same per-entry flags the batched device
+        solve uses (`sink_edge_flags`).  Entries the reference would assign that are not stored in M (scipy then
+        inserts explicit zeros) are left absent: same matrix values, and never the case on an MSI graph, whose
+        edges are stored in both directions (msi.py:64-66)."""
+        m = self.initial_M.copy()
+        if not m.has_sorted_indices:
+            m.sort_indices()
+        n = m.shape[0]
+        flag = sink_edge_flags(m, self._sink_pairs(msi))
+        rows = np.repeat(np.arange(n, dtype=np.int64), np.diff(m.indptr))
+        sel = np.zeros(n, dtype=bool)
+        sel[[msi.node2idx[t] for t in selected_drugs_and_indications]] = True
+        drop = ((flag & 1).astype(bool) & ~sel[rows]) | ((flag & 2).astype(bool) & sel[m.indices])
+        m.data[drop] = 0.0
+        return m
+
+    def refine_M_S(self, M):
+        """:49-56 — S = 1/rowsum(M) (0 stays 0), M <- diag(S)·M.  Row sums (numpy's reduceat order), reciprocals and
+        the scaling run on the device (gdr_rwr_refine_f64); returns (scipy csr_matrix, S ndarray) like the reference.
+        The returned structure is what scipy's `Q * M` leaves: zero products dropped, every row's entries in
+        reverse stored order (csr_matmat emits its linked list back to front), indices therefore unsorted."""
+        L = _ffi.lib()
+        dev = _device()
+        m = sp.csr_matrix(M, dtype=np.float64)
+        if not m.has_sorted_indices:
+            m = m.copy()
+            m.sort_indices()
+        n, nnz = m.shape[0], m.nnz
+        csr = DeviceCSR.from_scipy(m, dev, dtype=torch.float64)
+        s_dev = torch.empty(n, dtype=torch.float64, device=dev)
+        v_dev = torch.empty(max(nnz, 1), dtype=torch.float64, device=dev)[:nnz]
+        _ffi.check(L.gdr_rwr_refine_f64(_ffi.ptr(csr.rowptr), _ffi.ptr(csr.col), _ffi.ptr(csr.val), n, nnz,
+                                        _ffi.ptr(s_dev), _ffi.ptr(v_dev), _ffi.stream()), "rwr_refine_f64")
+        S = s_dev.cpu().numpy()
+        v = v_dev.cpu().numpy()
+        out = scaled_matrix_like_scipy(m, v)
+        return out, S
+
+    def power_iteration(self, M, S, nodelist, per_dict):
+        """:65-90 — personalised PageRank power iteration for one personalisation vector on a caller-supplied,
+        row-scaled M; returns the fp64 ndarray [N].  The iteration runs on the device (gdr_rwr_power_iteration_f64)
+        in the reference's accumulation order; `self.last_iterations` holds the iteration count.  Non-convergence
+        raises RuntimeError (the reference raises NetworkXError, an unimported name there: NameError in effect)."""
+        import ctypes
+        L = _ffi.lib()
+        dev = _device()
+        N = len(nodelist)
+        missing = set(nodelist) - set(per_dict)
+        if missing:
+            raise RuntimeError('Personalization dictionary must have a value for every node. Missing nodes %s' % missing)
+        p = np.array([per_dict[n] for n in nodelist], dtype=float)
+        m = sp.csr_matrix(M, dtype=np.float64)
+        if m.shape != (N, N):
+            raise RuntimeError(f"power_iteration: M is {m.shape}, nodelist has {N} entries")
+        csr_t = DeviceCSR.from_scipy(m, dev, dtype=torch.float64).transpose()      # x*M walks M.T, sources ascending
+        s_dev = torch.from_numpy(np.ascontiguousarray(np.asarray(S, dtype=np.float64))).to(dev)
+        p_dev = torch.from_numpy(p).to(dev)
+        x = torch.empty(N, dtype=torch.float64, device=dev)
+        ws = _ffi.workspace(L.gdr_rwr_power_iteration_workspace_bytes(N), dev)
+        iters = ctypes.c_int32(0)
+        _ffi.check(L.gdr_rwr_power_iteration_f64(_ffi.ptr(csr_t.rowptr), _ffi.ptr(csr_t.col), _ffi.ptr(csr_t.val), N,
+                                                 _ffi.ptr(s_dev), _ffi.ptr(p_dev), float(self.alpha), float(self.tol),
+                                                 int(self.max_iter), _ffi.ptr(x), ctypes.byref(iters), _ffi.ptr(ws),
+                                                 ws.numel(), _ffi.stream()), "rwr_power_iteration_f64")
+        self.last_iterations = int(iters.value)
+        return x.cpu().numpy()
+
     def get_personalization_dictionary(self, nodes_to_start_from, nodelist):
         personalization_dict = dict.fromkeys(nodelist, 0)
         N = len(nodes_to_start_from)

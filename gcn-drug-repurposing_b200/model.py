@@ -40,10 +40,31 @@ def _check_dense(t, name):
     return t.contiguous()
 
 
+def _check_layer_shapes(x, w1, b1, w2, b2, csr):
+    """The reference's nn.Linear(h, h) raises when hidden_units != feature width (model.py:142,165); the C ABI takes
+    bare pointers, so the same condition has to be checked here."""
+    if x.dim() != 2:
+        raise RuntimeError(f"features must be [n, d], got shape {tuple(x.shape)}")
+    n, d = x.shape
+    for nm, w in (("dense.weight", w1), ("dense2.weight", w2)):
+        if tuple(w.shape) != (d, d):
+            raise RuntimeError(f"{nm} has shape {tuple(w.shape)} but the features are {n}x{d}: hidden_units must "
+                               f"equal the feature width (the layer is Linear(h, h) applied to adj @ features)")
+    for nm, b in (("dense.bias", b1), ("dense2.bias", b2)):
+        if b.numel() != d:
+            raise RuntimeError(f"{nm} has {b.numel()} elements, expected {d}")
+    if csr.n_rows != n or csr.n_cols != n:
+        raise RuntimeError(f"adjacency is {csr.n_rows}x{csr.n_cols} but there are {n} feature rows")
+    for nm, t in (("dense.weight", w1), ("dense.bias", b1), ("dense2.weight", w2), ("dense2.bias", b2)):
+        if not t.is_cuda or t.dtype != torch.float32:
+            raise RuntimeError(f"{nm} must be an fp32 CUDA tensor (call model.cuda(); there is no CPU path)")
+
+
 def layer_forward_raw(csr, x, w1, b1, w2, b2, residual, decay):
     """One GSS_GNNLayer application (+ the residual update of the network loop).
     Returns P = Â·x, T = Â·(P⊙x), Z (pre-nonlinearity), Xnext (= ELU(Z) or residual + decay*ELU(Z))."""
     L = _ffi.lib()
+    _check_layer_shapes(x, w1, b1, w2, b2, csr)
     n, d = x.shape
     p, px = csr.spmm(x, out2_mul=x)      # model.py:163, and torch.mul(P, X) of :168 from the same launch
     t = csr.spmm(px)                     # model.py:169

@@ -1,5 +1,6 @@
 """Adam for the drop-in path: same constructor arguments, update rule and state layout as
-torch.optim.Adam (train.py:139-141: lr=3e-4, betas (0.9, 0.999), eps 1e-8, weight_decay 0, amsgrad False),
+torch.optim.Adam (train.py:139-141: lr=args.lr — 1e-4 by default, 3e-4 in train.sh — betas (0.9, 0.999), eps 1e-8,
+weight_decay 0, amsgrad False),
 but all parameter tensors are updated by ONE libgdr kernel (gdr_adam_step_multi_f32) instead of torch's
 foreach pipeline (7 launches per step at 4 tensors).  state_dict() is interchangeable with torch.optim.Adam's:
 per-parameter 'step' (0-d fp32 CPU tensor), 'exp_avg', 'exp_avg_sq'."""

@@ -16,50 +16,55 @@ import torch
 
 from .dataset import DiffusionDataLoader, DiffusionDataSet
 from .optim import Adam
-from .textio import savetxt_e18
+from .textio import read_node2vec_embs, savetxt_e18
 from .helper import (combine_graph, convert_sparse_matrix_to_sparse_tensor, gen_graph, gram_percentile,
                      preprocess_graph)
 from .model import GSS_loss, ResidualGraphConvolutionalNetwork
 
 
 def build_parser():
-    """train.py:12-58, flag for flag (defaults included)."""
+    """train.py:12-58, flag for flag with the reference's defaults.  `--gpu-id None` means CPU upstream
+    (train.py:68); this path has no CPU implementation, so None selects the current CUDA device.  `--dataset`,
+    `--data-path` and `--report-hard` are accepted and unused (they only feed the ransac graph modes, whose
+    datasets are absent upstream).  `--out-file` is an addition: train.py:193 hard-codes `graph_embs.txt`."""
     p = argparse.ArgumentParser(description='GCN similarity-loss embedding on a B200')
-    p.add_argument('--emb-file', type=str, required=True, help='node2vec-format .embs.txt (train.py:79)')
-    p.add_argument('--epochs', type=int, default=20)
-    p.add_argument('--lr', type=float, default=0.0001)
-    p.add_argument('--batch-size', type=int, default=0)
-    p.add_argument('--num-layers', type=int, default=2)
-    p.add_argument('--hidden-units', type=int, default=2048)
-    p.add_argument('--init-weights', type=float, default=1e-5)
-    p.add_argument('--layer-decay', type=float, default=0.3)
-    p.add_argument('--regularizer-scale', type=float, default=0.0)
-    p.add_argument('--k', type=int, default=5)
     p.add_argument('--kq', type=int, default=5)
-    p.add_argument('--alpha', type=float, default=1.0)
+    p.add_argument('--k', type=int, default=5)
+    p.add_argument('--alpha', type=float, default=1)
     p.add_argument('--beta', type=float, default=None)
     p.add_argument('--beta-percentile', type=float, default=None)
-    p.add_argument('--graph-mode', type=str, default='descriptor')
+    p.add_argument('--seed', type=int, default=None)
+    p.add_argument('--epochs', type=int, default=200)
+    p.add_argument('--batch-size', type=int, default=0)
+    p.add_argument('--hidden-units', type=int, default=128)
+    p.add_argument('--num-layers', type=int, default=2)
     p.add_argument('--loss', type=str, default='gss')
-    p.add_argument('--seed', type=int, default=0)
-    p.add_argument('--gpu-id', type=int, default=0)
+    p.add_argument('--lr', type=float, default=0.0001)
+    p.add_argument('--init-weights', type=float, default=1e-5)
+    p.add_argument('--regularizer-scale', type=float, default=1e-5)
+    p.add_argument('--layer-decay', type=float, default=0.3)
+    p.add_argument('--dataset', type=str, default='roxford5k', choices=['roxford5k', 'rparis6k', 'instre'])
+    p.add_argument('--emb-file', type=str, default=None, help='node2vec-format .embs.txt (train.py:79)')
+    p.add_argument('--data-path', type=str, default=None)
+    p.add_argument('--gpu-id', type=int, default=None)
+    p.add_argument('--report-hard', action='store_true')
+    p.add_argument('--graph-mode', type=str, default='descriptor', choices=['descriptor', 'ransac', 'approx_ransac'])
     p.add_argument('--out-file', type=str, default='graph_embs.txt', help="train.py:193 hard-codes this name")
     return p
 
 
 def load_embs(path):
-    """train.py:79-82: skip the 'N dim' header, drop the node-name column, fp64."""
-    with open(path) as f:
-        next(f)
-        rows = [np.array(line.split()[1:], dtype=np.float64) for line in f if line.strip()]
-    return np.stack(rows)
+    """train.py:79-82: skip the 'N dim' header, drop the node-name column, fp64.  Parsed by libgdr's host-side
+    reader (csrc/textio.cu) instead of np.loadtxt(dtype=object): same values, seconds instead of minutes at MSI scale."""
+    _names, vals = read_node2vec_embs(path)
+    return vals
 
 
 class GCNTrainer:
     """Model + optimizer + loss of train.py:111-150, features and adjacency resident on the device."""
 
     def __init__(self, features, adj, hidden_units, num_layers=2, layer_decay=0.3, init_weights=1e-5, alpha=1.0,
-                 lr=3e-4, batch_size=2048, beta=None, beta_percentile=None, device="cuda"):
+                 lr=1e-4, batch_size=2048, beta=None, beta_percentile=None, device="cuda"):
         self.device = torch.device(device)
         self.dataset = DiffusionDataSet(features=features, adj=adj.to(self.device))
         n = len(self.dataset)
@@ -69,7 +74,8 @@ class GCNTrainer:
                                                        init_weights=init_weights, layer_decay=layer_decay)
         self.model.to(self.device)
         self.model.train()
-        self.optimizer = Adam(self.model.parameters(), lr=lr, weight_decay=0)       # train.py:139-141
+        self.optimizer = Adam(self.model.parameters(), lr=lr, weight_decay=0)       # train.py:139-141 (lr: --lr,
+        #                                                                             default 1e-4; train.sh passes 3e-4)
         self.loss_fcn = GSS_loss(alpha).gss_loss
         self.beta = beta
         self.beta_percentile = beta_percentile
@@ -116,7 +122,13 @@ def main(args):
         raise Exception('beta and beta_percentile can not be used at the same time!')
     if args.graph_mode != 'descriptor':
         raise Exception('ransac graph modes need the retrieval datasets, absent from the reference repository too')
+    if args.emb_file is None:
+        raise Exception('--emb-file is required (train.py:79 reads it unconditionally)')
     ppi_embs = load_embs(args.emb_file)
+    if args.hidden_units != ppi_embs.shape[1]:
+        # upstream nn.Linear(h, h) raises a shape error on the first forward (model.py:142,165)
+        raise RuntimeError(f"--hidden-units {args.hidden_units} must equal the embedding width {ppi_embs.shape[1]} "
+                           "(the layer is Linear(h, h) applied to adj @ features)")
     X = ppi_embs.T                                   # (d, num_nodes)
     Q = X[:, 0:3]
     q_adj, q_features, x_adj, x_features = gen_graph(Q, X, args.kq, args.k, None, None)
@@ -127,7 +139,7 @@ def main(args):
     trainer = GCNTrainer(x_features, x_adj_normed_sparse_tensor, args.hidden_units, num_layers=args.num_layers,
                          layer_decay=args.layer_decay, init_weights=args.init_weights, alpha=args.alpha, lr=args.lr,
                          batch_size=args.batch_size, beta=args.beta, beta_percentile=args.beta_percentile,
-                         device=f"cuda:{args.gpu_id}")
+                         device="cuda" if args.gpu_id is None else f"cuda:{args.gpu_id}")
     if args.loss != 'gss':
         raise Exception("only the 'gss' loss is functional upstream (tri_loss references undefined names)")
     loader = trainer.loader(shuffle=True)

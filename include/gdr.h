@@ -270,6 +270,34 @@ int gdr_rwr_solve_f64(const int32_t *m_rowptr, const int32_t *m_col, const doubl
                       int64_t max_iter, double *x_out, int32_t *iters_out, void *workspace,
                       int64_t workspace_bytes, gdr_stream_t stream);
 
+/* The reference's per-seed methods with a caller-supplied matrix (one vector at a time):
+ *   refine_M_S(M) (diffusion_profiles.py:49-56): s_out[n] = 1/rowsum(M) in numpy's reduceat order (0 stays 0),
+ *       val_out[nnz] = s_out[row]*val (scipy's Q*M).  CSR rows sorted.
+ *   power_iteration(M, S, nodelist, per_dict) (:65-90): Mt = CSR of the transpose of the row-scaled M (sources
+ *       ascending, gdr_csr_transpose), s = the S above (only S == 0 matters), p[n] = per_dict values in nodelist
+ *       order (normalised on the device, p / p.sum()).  x_out[n] device; *iters_out_host = iterations used.
+ *       Synchronises the stream every iteration; GDR_E_NOCONV after max_iter iterations (the reference raises, :90). */
+int gdr_rwr_refine_f64(const int32_t *rowptr, const int32_t *col, const double *val, int64_t n, int64_t nnz,
+                       double *s_out, double *val_out, gdr_stream_t stream);
+int64_t gdr_rwr_power_iteration_workspace_bytes(int64_t n);
+int gdr_rwr_power_iteration_f64(const int32_t *mt_rowptr, const int32_t *mt_col, const double *mt_val, int64_t n,
+                                const double *s, const double *p, double alpha, double tol, int64_t max_iter,
+                                double *x_out, int32_t *iters_out_host, void *workspace, int64_t workspace_bytes,
+                                gdr_stream_t stream);
+
+/* ---- consumer ranking step (predict_drug.py:49-74,111-124; run_covid.py:294-306) ----------------------------- *
+ * fp64 like the reference (np.loadtxt).  embs: [n, d] row-major.  prox_out[i] = <normalize(embs[sel[i]]),
+ * normalize(embs[query_row])> (sklearn normalize: a zero norm divides by 1) when normalize != 0, else the raw dot
+ * product (np.matmul(drug_embs, covid_emb)).  order_out[j] = position i into sel of the j-th largest score
+ * (np.argsort(proximities)[::-1]; ties keep ascending position), sorted_out[j] (optional) = that score.
+ * sel == NULL: rows 0..m-1.  gdr_rank_values_f64: values_out[i] = values[sel[i]] and its descending order.        */
+int64_t gdr_rank_workspace_bytes(int64_t m);
+int gdr_rank_embedding_f64(const double *embs, int64_t n, int64_t d, int normalize, int64_t query_row,
+                           const int32_t *sel, int64_t m, double *prox_out, int32_t *order_out, double *sorted_out,
+                           void *workspace, int64_t workspace_bytes, gdr_stream_t stream);
+int gdr_rank_values_f64(const double *values, const int32_t *sel, int64_t m, double *values_out, int32_t *order_out,
+                        double *sorted_out, void *workspace, int64_t workspace_bytes, gdr_stream_t stream);
+
 /* ---- host-side text formats around the path (no device work) ------------------------------------------ *
  * graph_embs.txt exactly as np.savetxt(fname, hidden_emb) writes it (train.py:193; '%.18e', ' ', '\n', no header):
  * returns the bytes written or a negative GDR_E_* code.  x is a HOST array [n, d] of fp32 (4) or fp64 (8).      */

@@ -231,6 +231,7 @@ def main():
     gcn_case("edge300_d256", ref_model, ref_helper, n=300, d=256, k=5, batch=128, num_layers=2, seed=3,
              adjacency="edge", lean=True)
     rwr_case("msi600", DiffusionProfiles, counters, scale=0.02, seed=5, n_seeds=48)
+    gcn_case("knn2000", ref_model, ref_helper, n=2000, d=128, k=5, batch=512, num_layers=2, seed=4, lean=True)
     print("golden fixtures written; oracle == reference on every compared tensor")
 
 

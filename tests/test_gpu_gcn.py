@@ -64,7 +64,7 @@ def test_csr_transpose_matches_scipy(gdr, n_rows, n_cols, density):
     assert np.array_equal(t.val.cpu().numpy(), mt.data)
 
 
-@pytest.mark.parametrize("case", ["gcn_knn257.npz", "gcn_knn600_l3.npz", "gcn_edge300_d256.npz"])
+@pytest.mark.parametrize("case", ["gcn_knn257.npz", "gcn_knn600_l3.npz", "gcn_edge300_d256.npz", "gcn_knn2000.npz"])
 def test_preprocess_graph_matches_reference(gdr, case):
     g = load_golden(case)
     n = len(g["x_adj_indptr"]) - 1
@@ -212,11 +212,15 @@ def _assert_close_after_adam(actual, expected, lr, what):
     a, e = np.asarray(actual, np.float64), np.asarray(expected, np.float64)
     err = np.abs(a - e)
     strict = (err <= 1e-6) | (err <= 1e-5 * np.abs(e))
+    print(f"\n[{what}] strict north_star tolerance holds for {strict.mean():.6f} of {strict.size} entries, "
+          f"max abs err {err.max():.3e}")
+    # 1st assertion: the north_star tolerance, on at least 99.99 % of the entries
     assert strict.mean() >= 0.9999, f"{what}: only {strict.mean():.6f} of the entries within 1e-5 rel / 1e-6 abs"
+    # 2nd, explicit and relaxed: the remaining near-cancellation entries stay within 1e-2*lr
     assert err.max() <= 1e-2 * lr, f"{what}: max abs err {err.max():.3e} exceeds 1e-2*lr"
 
 
-@pytest.mark.parametrize("case", ["gcn_knn257.npz", "gcn_knn600_l3.npz", "gcn_edge300_d256.npz"])
+@pytest.mark.parametrize("case", ["gcn_knn257.npz", "gcn_knn600_l3.npz", "gcn_edge300_d256.npz", "gcn_knn2000.npz"])
 def test_training_steps_match_reference(gdr, case):
     """train.py:155-184 driven through the drop-in classes: forward, loss, backward, torch Adam, 3 steps."""
     g = load_golden(case)
@@ -296,7 +300,7 @@ def test_cpu_tensors_are_rejected(gdr):
 
 
 # ---- Gram reductions: kNN graph (gen_graph) and the beta percentile -----------------------------------
-@pytest.mark.parametrize("case", ["gcn_knn257.npz", "gcn_knn600_l3.npz"])
+@pytest.mark.parametrize("case", ["gcn_knn257.npz", "gcn_knn600_l3.npz", "gcn_knn2000.npz"])
 def test_gen_graph_matches_reference(gdr, case):
     g = load_golden(case)
     n, d = g["embs"].shape
@@ -343,7 +347,7 @@ def test_gram_percentile_vs_numpy(gdr, n, d, q):
     assert_close(got, exp, what=f"beta q={q}")
 
 
-@pytest.mark.parametrize("case", ["gcn_knn257.npz", "gcn_knn600_l3.npz", "gcn_edge300_d256.npz"])
+@pytest.mark.parametrize("case", ["gcn_knn257.npz", "gcn_knn600_l3.npz", "gcn_edge300_d256.npz", "gcn_knn2000.npz"])
 def test_beta_selection_matches_reference(gdr, case):
     g = load_golden(case)
     n, d = g["embs"].shape

@@ -1,0 +1,206 @@
+"""GPU parity tests on the REAL multiscale interactome (no-PPI MSI: 22,550 nodes / 182,204 directed edges; covid
+variant: 20,228 nodes, NodeCovid the only indication), against fixtures the reference itself produced
+(oracle/gen_golden_msi.py -> tests/golden/*).  The drop-in classes are fed a real networkx.DiGraph.
+
+Tolerances: iteration counts and index structures exact; fp64 profiles <= 1e-12 relative (north_star asks 1e-5);
+fp32 activations / gradients / losses <= 1e-5 relative or 1e-6 absolute; ranks exact outside ties."""
+import numpy as np
+import pytest
+import scipy.sparse as sp
+import torch
+
+from .conftest import assert_close, load_golden
+from .msi_fixture import GoldenMSI
+from oracle import rwr_oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def _dp(gdr, path=None):
+    return gdr.DiffusionProfiles(alpha=gdr.synth.RWR_ALPHA, max_iter=gdr.synth.RWR_MAX_ITER, tol=gdr.synth.RWR_TOL,
+                                 weights=gdr.synth.MSI_WEIGHTS, num_cores=4, save_load_file_path=path)
+
+
+@pytest.mark.parametrize("name", ["msi_noppi", "msi_covid"])
+def test_diffusion_profiles_on_real_msi_match_reference(gdr, name):
+    msi = GoldenMSI(f"{name}_graph.npz")
+    r = load_golden(f"rwr_{name}.npz")
+    dp = _dp(gdr)
+    dp.get_initial_M(msi)                                            # iterates a real nx.DiGraph
+    g = msi.arrays
+    m0 = rwr_oracle.initial_matrix(len(msi.nodelist), g["src"], g["dst"], g["weight"])
+    assert (dp.initial_M != m0).nnz == 0
+    seeds = [str(s) for s in r["seed_names"]]
+    assert len(seeds) >= 64
+    x, iters = dp.solve(msi, seeds)
+    assert np.array_equal(iters, r["iters"])                         # per-seed stopping iteration: exact
+    np.testing.assert_allclose(x[:, r["sample_idx"]], r["profiles_sampled"], rtol=1e-12, atol=1e-300)
+    np.testing.assert_allclose(np.take_along_axis(x, r["top_idx"].astype(np.int64), 1), r["top_val"], rtol=1e-12)
+    nf = r["profiles_full"].shape[0]
+    np.testing.assert_allclose(x[:nf], r["profiles_full"], rtol=1e-12, atol=1e-300)
+    same = (x[:nf] == r["profiles_full"]).mean()
+    print(f"\n[{name}] bit-identical profile entries: {same:.6f}")
+    assert same > 0.999
+    np.testing.assert_allclose(x.sum(axis=1), r["sums"], rtol=1e-12)
+
+
+@pytest.mark.parametrize("name,rows", [("msi_noppi", (0, 7, 33)), ("msi_covid", (2, 63))])
+def test_per_seed_methods_replay_calculate_diffusion_profile(gdr, name, rows):
+    """diffusion_profiles.py:103-110 call by call through the drop-in's per-seed methods."""
+    msi = GoldenMSI(f"{name}_graph.npz")
+    r = load_golden(f"rwr_{name}.npz")
+    dp = _dp(gdr)
+    dp.get_initial_M(msi)
+    sp_idx = msi.seed_proteins_by_index()
+    sinks = [int(s) for s in msi.arrays["seeds"]]
+    for row in rows:
+        nm = str(r["seed_names"][row])
+        M = dp.convert_M_to_make_all_drugs_indications_sinks_except_selected(msi, [nm])
+        o_m = rwr_oracle.seed_matrix(dp.initial_M, msi.node2idx[nm], sp_idx, sinks)
+        assert np.array_equal(M.indptr, o_m.indptr) and np.array_equal(M.indices, o_m.indices)
+        assert np.array_equal(M.data, o_m.data)                      # explicit zeros kept, same positions
+        M2, S = dp.refine_M_S(M)
+        o_m2, o_s = rwr_oracle.refine(o_m)
+        assert isinstance(M2, sp.csr_matrix) and isinstance(S, np.ndarray)
+        assert np.array_equal(S, o_s)                                # reduceat order reproduced: bit-exact
+        assert np.array_equal(M2.indptr, o_m2.indptr) and np.array_equal(M2.indices, o_m2.indices)
+        assert np.array_equal(M2.data, o_m2.data)
+        per = dp.get_personalization_dictionary([nm], msi.nodelist)
+        x = dp.power_iteration(M2, S, msi.nodelist, per)
+        assert isinstance(x, np.ndarray) and x.dtype == np.float64 and x.shape == (len(msi.nodelist),)
+        assert dp.last_iterations == int(r["iters"][row])
+        np.testing.assert_allclose(x[r["sample_idx"]], r["profiles_sampled"][row], rtol=1e-12, atol=1e-300)
+        np.testing.assert_allclose(x[r["top_idx"][row]], r["top_val"][row], rtol=1e-12)
+        if row < r["profiles_full"].shape[0]:
+            np.testing.assert_allclose(x, r["profiles_full"][row], rtol=1e-12, atol=1e-300)
+            assert (x == r["profiles_full"][row]).mean() > 0.999
+
+
+def test_power_iteration_general_personalisation_and_errors(gdr):
+    """A multi-node personalisation dictionary (1/N each, :58-63) and the failure modes."""
+    msi = GoldenMSI("msi_covid_graph.npz")
+    dp = _dp(gdr)
+    dp.get_initial_M(msi)
+    picks = [msi.drugs_in_graph[3], msi.drugs_in_graph[100], "NodeCovid"]
+    M, S = dp.refine_M_S(dp.convert_M_to_make_all_drugs_indications_sinks_except_selected(msi, picks))
+    per = dp.get_personalization_dictionary(picks, msi.nodelist)
+    x = dp.power_iteration(M, S, msi.nodelist, per)
+    # the reference's arithmetic (oracle) with the same vector
+    n = len(msi.nodelist)
+    p = np.array([per[k] for k in msi.nodelist], dtype=float)
+    p = p / p.sum()
+    dang = np.where(S == 0)[0]
+    xo = np.repeat(1.0 / n, n)
+    for it in range(1, 1001):
+        xl = xo
+        xo = dp.alpha * (xo * M + sum(xo[dang]) * p) + (1 - dp.alpha) * p
+        if np.absolute(xo - xl).sum() < n * dp.tol:
+            break
+    assert dp.last_iterations == it
+    np.testing.assert_allclose(x, xo, rtol=1e-12, atol=1e-300)
+    dp.max_iter = 2
+    with pytest.raises(RuntimeError, match="failed to converge"):
+        dp.power_iteration(M, S, msi.nodelist, per)
+    del per[msi.nodelist[5]]
+    with pytest.raises(RuntimeError, match="Missing nodes"):
+        dp.power_iteration(M, S, msi.nodelist, per)
+
+
+def test_gcn_training_on_real_msi_edgelist_matches_reference(gdr):
+    """train.py:99-184 with the real no-PPI MSI weighted edgelist as the adjacency (asymmetric Â: the backward pass
+    runs on the explicit transposed CSR), 3 Adam steps, against the reference-generated golden."""
+    gr = load_golden("msi_noppi_graph.npz")
+    g = load_golden("gcn_msi_noppi_edge.npz")
+    n, d = len(gr["names"]), int(g["d"])
+    a = sp.csr_matrix((gr["weight"], (gr["src"].astype(np.int64), gr["dst"].astype(np.int64))), shape=(n, n))
+    a_hat = gdr.preprocess_graph(a)
+    assert np.array_equal(a_hat.indptr, g["ahat_indptr"]) and np.array_equal(a_hat.indices, g["ahat_indices"])
+    f32_same = a_hat.data.astype(np.float32) == g["ahat_data_f32"]
+    assert f32_same.mean() > 0.9999
+    adj = gdr.convert_sparse_matrix_to_sparse_tensor(a_hat).cuda()
+    x = torch.from_numpy(gdr.synth.synth_embeddings(n, d, seed=int(g["seed"]))).cuda()
+    model = gdr.ResidualGraphConvolutionalNetwork(2048, n, num_layers=2, hidden_units=d, layer_decay=0.3)
+    with torch.no_grad():
+        model.gcn_layer.dense.weight.copy_(torch.from_numpy(g["w_init"]))
+        model.gcn_layer.dense2.weight.copy_(torch.from_numpy(g["w_init"]))
+    model = model.cuda()
+    opt = torch.optim.Adam(model.parameters(), lr=float(g["lr"]), weight_decay=0)
+    loss_fcn = gdr.GSS_loss(1.0).gss_loss
+    offs = np.concatenate([[0], np.cumsum(g["batch_sizes"])])
+    rows = g["rows_kept"]
+    losses = []
+    for it in range(len(g["batch_sizes"])):
+        h = model(x=x, adj=adj)
+        if it == 0:
+            beta = gdr.helper.gram_percentile(h.detach(), float(g["beta_percentile"]))
+            assert_close(beta, g["beta"], what="beta on the real MSI (train.py:166-167)")
+            assert_close(h.detach().cpu().numpy()[rows], g["h_step0_rows"], what="hidden_emb rows step0")
+        loss = loss_fcn(embs=h, beta=float(g["beta"]),
+                        index=torch.from_numpy(g["batches_flat"][offs[it]:offs[it + 1]]).cuda())
+        opt.zero_grad()
+        loss.backward()
+        tag = "step0" if it == 0 else ("last" if it == len(g["batch_sizes"]) - 1 else None)
+        if tag:
+            for nm, p in zip(("dw1", "db1", "dw2", "db2"), model.parameters()):
+                assert_close(p.grad.cpu().numpy(), g[f"{nm}_{tag}"], what=f"{nm} {tag}")
+        if tag == "last":
+            assert_close(h.detach().cpu().numpy()[rows], g["h_last_rows"], what="hidden_emb rows last")
+        opt.step()
+        losses.append(loss.item())
+    assert_close(np.array(losses), g["losses"], what="losses")
+
+
+def test_consumer_ranking_matches_reference(gdr):
+    """predict_drug.py:49-74,111-124 and run_covid.py:294-306 on the covid-variant MSI."""
+    from gdr_b200 import ranking
+    msi = GoldenMSI("msi_covid_graph.npz", "rank_covid.npz")
+    r = load_golden("rank_covid.npz")
+    names = msi.nodelist
+    embs = gdr.synth.synth_embeddings(len(names), int(r["d"]), seed=int(r["emb_seed"])).astype(np.float64)
+    named, ranked, prox = ranking.drug_proximity_ranking(names, embs, msi, query="NodeCovid", gcn=True)
+    np.testing.assert_allclose(prox, r["drug_proximities_ranked"], rtol=1e-12, atol=1e-15)
+    got_rows = np.array([msi.node2idx[x] for x in ranked])
+    exp = r["drug_proximities_ranked"]
+    clear = np.concatenate([[True], np.abs(np.diff(exp)) > 1e-13]) & np.concatenate([np.abs(np.diff(exp)) > 1e-13, [True]])
+    assert clear.mean() > 0.99
+    assert np.array_equal(got_rows[clear], r["drug_ranked_rows"][clear])             # ranks exact outside ties
+    assert [str(x) for x in named[:20]] == [str(x) for x in r["drugs_name_ranked_head"]]
+    pnames, pprox = ranking.protein_proximity_table(names, embs, msi)
+    assert [str(x) for x in pnames] == [str(x) for x in r["protein_names"]]
+    np.testing.assert_allclose(np.array(pprox), r["protein_proximities"], rtol=1e-12, atol=1e-15)
+    _n2, d_ranked, d_vals = ranking.diffusion_drug_ranking(r["covid_profile"], msi)
+    assert np.array_equal(d_vals, r["diffusion_values_ranked"])                      # a gather + sort: bit-exact
+    exp_v = r["diffusion_values_ranked"]
+    clear = np.concatenate([[True], np.diff(exp_v) != 0]) & np.concatenate([np.diff(exp_v) != 0, [True]])
+    assert np.array_equal(np.array([msi.node2idx[x] for x in d_ranked])[clear], r["diffusion_ranked_rows"][clear])
+
+
+def test_ranking_edge_cases(gdr):
+    from gdr_b200 import ranking
+    e = np.zeros((5, 8))
+    e[1, 0] = 2.0
+    e[2, :] = 1.0
+    e[3, 0] = -1.0
+    order, prox = ranking.rank_by_embedding(e, 1, [0, 2, 3, 1], normalize=True)    # row 0 has zero norm: stays 0
+    np.testing.assert_allclose(prox, [0.0, 1 / np.sqrt(8), -1.0, 1.0], rtol=1e-15)
+    assert order.tolist() == [3, 1, 0, 2]
+    order, vals = ranking.rank_values(np.array([0.5, np.inf, -1.0, 0.5]), None)
+    assert order.tolist() == [1, 0, 3, 2] and vals.tolist() == [0.5, np.inf, -1.0, 0.5]
+    order, prox = ranking.rank_by_embedding(e, 1, [], normalize=False)
+    assert order.size == 0 and prox.size == 0
+    with pytest.raises(IndexError):
+        ranking.rank_by_embedding(e, 1, [7])
+
+
+def test_width_mismatch_raises_like_nn_linear(gdr):
+    """hidden_units != feature width: the reference's nn.Linear(h, h) raises; so must the drop-in."""
+    adj = gdr.convert_sparse_matrix_to_sparse_tensor(sp.identity(16, format="csr")).cuda()
+    for hidden, width in ((256, 128), (64, 128)):
+        model = gdr.ResidualGraphConvolutionalNetwork(1, 1, num_layers=2, hidden_units=hidden).cuda()
+        with pytest.raises(RuntimeError, match="hidden_units"):
+            model(torch.randn(16, width, device="cuda"), adj)
+        with pytest.raises(RuntimeError, match="hidden_units"):
+            model.gcn_layer(torch.randn(16, width, device="cuda"), adj)
+    model = gdr.ResidualGraphConvolutionalNetwork(1, 1, num_layers=2, hidden_units=128).cuda()
+    with pytest.raises(RuntimeError, match="feature rows"):
+        model(torch.randn(17, 128, device="cuda"), adj)

@@ -34,6 +34,7 @@ def test_rmat_spmm_sampled_rows_against_fp64(rmat):
     deg = np.diff(rp)
     rng = np.random.default_rng(0)
     rows = np.unique(np.concatenate([rng.integers(0, csr.n_rows, 48), np.argsort(deg)[-8:], np.argsort(deg)[:4]]))
+    n_strict = n_all = 0
     for r in rows:                                         # hubs (chunked path), ordinary and shortest rows
         s, e = rp[r], rp[r + 1]
         c = csr.col[s:e].long()
@@ -41,7 +42,13 @@ def test_rmat_spmm_sampled_rows_against_fp64(rmat):
         ref = (w[:, None] * x[c].double()).sum(0).cpu().numpy()
         scale = (w[:, None].abs() * x[c].double().abs()).sum(0).cpu().numpy()
         err = np.abs(y[r].double().cpu().numpy() - ref)
+        n_strict += int(((err <= 1e-6) | (err <= 1e-5 * np.abs(ref))).sum())
+        n_all += err.size
+        # explicit, relaxed: fp32 summation of up to ~10^5 terms against the exact sum, scaled by sum |w||x|
         assert (err <= 1e-6 + 3e-7 * scale).all(), f"row {r} (degree {e - s}): max err {err.max():.3e}"
+    print(f"\n[rmat sampled rows] north_star tolerance (1e-5 rel / 1e-6 abs vs fp64) holds for "
+          f"{n_strict / n_all:.6f} of {n_all} entries")
+    assert n_strict / n_all >= 0.99
 
 
 def test_rmat_spmm_linearity_and_determinism(rmat):
@@ -90,9 +97,7 @@ def test_msi_scale_training_iteration_against_oracle(gdr):
     for p, q, nm in zip(tr.model.parameters(), o_grads, ("dW1", "db1", "dW2", "db2")):
         got, ref = p.grad.cpu().numpy().astype(np.float64), q.numpy().astype(np.float64)
         err = np.abs(got - ref)
-        # every entry sums ~30k signed products: entries that cancel to ~0 carry the rounding noise of the large
-        # ones, in the reference's own fp32 sum as much as here, so the absolute floor scales with the tensor
-        ok = (err <= 1e-6) | (err <= 1e-5 * np.abs(ref)) | (err <= 1e-5 * np.abs(ref).max())
-        assert ok.all(), f"{nm} at MSI scale: max abs err {err.max():.3e} (max |ref| {np.abs(ref).max():.3e})"
         strict = (err <= 1e-6) | (err <= 1e-5 * np.abs(ref))
         print(f"\n[{nm}] within 1e-5 rel / 1e-6 abs: {strict.mean():.6f} of entries, max abs err {err.max():.3e}")
+        assert strict.all(), (f"{nm} at MSI scale: {int((~strict).sum())} entries outside 1e-5 rel / 1e-6 abs, "
+                              f"max abs err {err.max():.3e} (max |ref| {np.abs(ref).max():.3e})")
