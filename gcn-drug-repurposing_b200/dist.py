@@ -23,8 +23,11 @@ exchange step the path really has.
 Classes, in the order they were measured (DESIGN.md §4 has the numbers):
     RowPartitionedSpMM   the design above (pull only, NCCL all-to-all)
     LShapedSpMM          blocks above the diagonal are multiplied at the column owner and their partial rows
-                         sent back; transport "nccl" or "p2p" (gdr_push_rows_f32 into peer symmetric memory)
-    NvlsLShapedSpMM      the same with NVSwitch multicast / in-switch reduction for the hub ranks
+                         sent back; transport "nccl" or "p2p" (gdr_push_rows_f32 into peer symmetric memory);
+                         options hub_first / split_pull reorder the step around rank 0's link (the critical path)
+(An NVSwitch-multicast variant for the hub ranks - multimem.st broadcast of their X block, multimem.ld_reduce of
+their partial rows - was measured in round 1 at 8.55 ms against 7.28 ms per step and removed; the two multimem
+kernels stay in csrc/p2p.cu as tested primitives.)
 """
 import numpy as np
 import torch
@@ -306,11 +309,21 @@ class LShapedSpMM:
     """
 
     def __init__(self, local_csr, bounds, rank, world, d, group=None, comm_stream=None, group_partials=None,
-                 transport="nccl", push_ctas=0):
+                 transport="nccl", push_ctas=0, hub_first=False, split_pull=False):
         """group_partials: a second communicator for the partial-row exchange, so that it can run while the
         X-row exchange is still in flight (opposite directions on full-duplex links); default: `group`.
         transport: "nccl" (all_to_all of packed rows) or "p2p" (gdr_push_rows_f32: rows are stored straight into
-        the destination's receive region over NVLink; buffers live in symmetric memory)."""
+        the destination's receive region over NVLink; buffers live in symmetric memory).
+        p2p only (both change the order of launches, not the arithmetic of any output row's partial sums):
+          hub_first   the push product runs in two launches, the block whose partial rows go to rank 0 first, and
+                      those rows leave as soon as it is done: rank 0 receives the most partial rows (its link is
+                      the critical path of the partial exchange) and no longer waits for the whole push product.
+          split_pull  the pull product is cut by SOURCE of the gathered X rows: "early" = own columns and rows of
+                      ranks 1..s-1, "late" = rows of rank 0 (the hub block everybody references; its owner is the
+                      last sender to finish).  Arrival is signalled per source (symmetric-memory put/wait_signal
+                      instead of one barrier), the early product starts when ranks 1..s-1 have delivered, and the
+                      late product is folded into the final add pass (same kernel, one pass over Y).  True: only
+                      where an add pass exists; "force": also as an extra in-place pass (tests, 2-GPU runs)."""
         self.bounds = [int(b) for b in bounds]
         self.rank, self.world, self.d, self.group = rank, world, d, group
         self.group_partials = group_partials if group_partials is not None else group
@@ -333,6 +346,9 @@ class LShapedSpMM:
         self.xrecv_splits = [int(t.numel()) for t in need_from]
         n_xrecv = int(sum(self.xrecv_splits))
         self.pull = csr_from_sorted_rows(krow, new_col, kval, self.n_own, self.n_own + n_xrecv)
+        # entries that gather rows received from rank 0 (they sit first in the receive region)
+        self._late_mask = (new_col >= self.n_own) & (new_col < self.n_own + self.xrecv_splits[0]) if s > 0 else None
+        self._pull_parts = (krow, new_col, kval)
         want = torch.cat(need_from) if n_xrecv else torch.zeros(0, dtype=torch.int64, device=dev)
         self.send_idx, self.xsend_splits = _a2a_var(want, self.xrecv_splits, group)
 
@@ -359,18 +375,27 @@ class LShapedSpMM:
         o2 = torch.argsort(add_rows, stable=True)                         # by row; sources stay in rank order
         self.add = csr_from_sorted_rows(add_rows[o2], pos[o2], torch.ones(self.n_precv, dtype=val.dtype, device=dev),
                                         self.n_own, max(self.n_precv, 1))
+        self._add_parts = (add_rows[o2], pos[o2])
         del src
+        # rows of the push product whose partial rows go to rank 0 come first (psend is stacked by destination)
+        self.n_psend_hub = self.psend_splits[0] if s > 0 else 0
 
         # ---- per-step buffers ---------------------------------------------------------------------------
         f = dict(dtype=val.dtype, device=dev)
         self.p2p = transport == "p2p"
         self.push_ctas = int(push_ctas)
+        self.hub_first = bool(hub_first) and self.p2p and world > 2
+        self.split_pull = split_pull if (self.p2p and world > 1) else False
+        self._split_requested = self.split_pull                           # same value on every rank
+        self._push_slices = {}
         if self.p2p:
             self._setup_p2p(n_xrecv, f)
+            self._setup_split(val)
         else:
             self.xbuf = torch.empty(self.n_own + n_xrecv, d, **f)
             self.precv = torch.empty(max(self.n_precv, 1), d, **f)[:self.n_precv]
             self.xsend = torch.empty(int(self.send_idx.numel()), d, **f)
+        self._pull_parts = self._add_parts = self._late_mask = None        # construction-time index lists
         self.x_own, self.x_recv = self.xbuf[:self.n_own], self.xbuf[self.n_own:]
         self.psend = torch.empty(self.n_psend, d, **f)
         self.y = torch.empty(self.n_own, d, **f)
@@ -424,6 +449,43 @@ class LShapedSpMM:
                 poff[a], pcnt[a] = off, c
             off += c
         self._ppush = (arr(*pdst), arr(*([None] * world)), i64(*poff), i64(*pcnt))
+        # hub-first variant: destination 0 alone, then the rest
+        hub_cnt = [pcnt[0]] + [0] * (world - 1)
+        rest_cnt = [0] + pcnt[1:]
+        self._ppush_hub = (arr(*pdst), arr(*([None] * world)), i64(*poff), i64(*hub_cnt))
+        self._ppush_rest = (arr(*pdst), arr(*([None] * world)), i64(*poff), i64(*rest_cnt))
+        self._xrows_max = xrows_max
+        self._x_sources = [r for r in range(world) if self.xrecv_splits[r] > 0]
+        self._x_dests = [r for r in range(world) if self.xsend_splits[r] > 0]
+
+    def _setup_split(self, val):
+        """split_pull: pull_early (own columns + rows of ranks 1..s-1), and `final` = [late pull entries | partial-row
+        adds] as ONE CSR over the symmetric buffer (xbuf and precv live in the same allocation), so that the late
+        product costs no extra pass over Y.  Entry order inside a row: late pull entries by ascending column, then
+        the partial rows by source rank - fixed, so the result is deterministic."""
+        self.pull_early = self.pull_late = self.final = None
+        if not self.split_pull or self.rank == 0 or self.xrecv_splits[0] == 0:
+            self.split_pull = False
+            return
+        if self.split_pull != "force" and self.n_precv == 0:
+            self.split_pull = False                       # no add pass to fold the late product into
+            return
+        krow, new_col, kval = self._pull_parts
+        late = self._late_mask
+        dev = krow.device
+        n_cols = self.n_own + int(sum(self.xrecv_splits))
+        self.pull_early = csr_from_sorted_rows(krow[~late], new_col[~late], kval[~late], self.n_own, n_cols)
+        if self.n_precv:
+            add_rows, add_pos = self._add_parts
+            rows = torch.cat([krow[late], add_rows])
+            cols = torch.cat([new_col[late], add_pos + self._xrows_max])
+            vals = torch.cat([kval[late], torch.ones(self.n_precv, dtype=val.dtype, device=dev)])
+            order = torch.argsort(rows, stable=True)      # late entries stay ahead of the adds inside every row
+            self.final = csr_from_sorted_rows(rows[order], cols[order], vals[order], self.n_own,
+                                              self._xrows_max + self.n_precv)
+            self._buf_all = self._symm_t.view(-1, self.d)[:self._xrows_max + self.n_precv]
+        else:
+            self.pull_late = csr_from_sorted_rows(krow[late], new_col[late], kval[late], self.n_own, n_cols)
 
     def _push(self, src, table):
         dst, idx, off, cnt = table
@@ -439,33 +501,72 @@ class LShapedSpMM:
         return cls(local, bounds, rank, world, d, group, group_partials=group_partials, **kw)
 
     # the two exchanges, separately callable (tests replace the device products around them)
+    SIG_X = 4                                       # signal-pad channel of the per-source X arrival flags
+
     def exchange_x(self):
+        """Returns (ev_early, ev_late): events on the current stream after which the rows of ranks 1..s-1 / of every
+        source have landed in xbuf.  Without split_pull both are the same event (one barrier)."""
         if self.p2p:
+            cur = torch.cuda.current_stream()
             self._hdl.barrier(channel=0)            # every rank is done reading last step's xbuf / precv
-            self._ev_b0 = torch.cuda.current_stream().record_event()
+            self._ev_b0 = cur.record_event()
             if self.send_idx.numel():
                 self._push(self.x_own, self._xpush)
+            if self._signals:
+                for r in self._x_dests:             # my rows for r have landed (kernel completion orders the stores)
+                    self._hdl.put_signal(r, channel=self.SIG_X)
+                for r in self._x_sources:
+                    if r != 0:
+                        self._hdl.wait_signal(r, channel=self.SIG_X)
+                ev_early = cur.record_event()
+                if 0 in self._x_sources:
+                    self._hdl.wait_signal(0, channel=self.SIG_X)
+                return ev_early, cur.record_event()
             self._hdl.barrier(channel=1)            # every rank's rows have landed
-            return
+            ev = cur.record_event()
+            return ev, ev
         if self.xsend.numel():
             _ffi.check(_ffi.lib().gdr_gather_rows_f32(_ffi.ptr(self.x_own), _ffi.ptr(self.send_idx),
                                                       self.send_idx.numel(), self.n_own, self.d,
                                                       _ffi.ptr(self.xsend), _ffi.stream()), "gather_rows")
         dist.all_to_all_single(self.x_recv, self.xsend, self.xrecv_splits, self.xsend_splits, group=self.group)
+        ev = torch.cuda.current_stream().record_event() if self.x_own.is_cuda else None
+        return ev, ev
+
+    @property
+    def _signals(self):
+        """Per-source arrival signals replace barrier 1 when ANY rank splits its pull product (collective choice:
+        the option is the same on every rank, and a sender cannot know which receivers fold their late part)."""
+        return bool(self._split_requested)
 
     def push_product(self):
         if self.n_psend:
             self.push.spmm(self.x_own, out=self.psend)                    # needs only the own X block
 
+    def _push_product_rows(self, lo, hi):
+        """Rows [lo, hi) of the push product (a row slice of the same CSR: same kernel, same per-row arithmetic)."""
+        if hi <= lo:
+            return
+        key = (lo, hi)
+        sub = self._push_slices.get(key)
+        if sub is None:
+            rp = self.push.rowptr
+            p0, p1 = int(rp[lo].item()), int(rp[hi].item())
+            sub = DeviceCSR((rp[lo:hi + 1] - p0).contiguous(), self.push.col[p0:p1], self.push.val[p0:p1], hi - lo,
+                            self.push.n_cols)
+            self._push_slices[key] = sub
+        sub.spmm(self.x_own, out=self.psend[lo:hi])
+
     def hub_reduce(self):
         pass                                                              # (NvlsLShapedSpMM only)
 
-    def exchange_partials(self):
+    def exchange_partials(self, table=None, last=True):
         if self.p2p:
             torch.cuda.current_stream().wait_event(self._ev_b0)
             if self.n_psend:
-                self._push(self.psend, self._ppush)
-            self._hdl.barrier(channel=2)
+                self._push(self.psend, table if table is not None else self._ppush)
+            if last:
+                self._hdl.barrier(channel=2)
             return
         dist.all_to_all_single(self.precv, self.psend, self.precv_splits, self.psend_splits,
                                group=self.group_partials)
@@ -478,239 +579,46 @@ class LShapedSpMM:
         cs, cs2 = self.comm_stream, self.comm_stream2
         cs.wait_stream(cur)
         with torch.cuda.stream(cs):
-            self.exchange_x()
-            ev_x = cs.record_event()
-        self.push_product()
-        ev_p = cur.record_event()
-        with torch.cuda.stream(cs2):
-            cs2.wait_event(ev_p)
-            self.exchange_partials()
-            ev_y = cs2.record_event()
+            ev_early, ev_late = self.exchange_x()
+        if self.hub_first and self.n_psend_hub and self.n_psend_hub < self.n_psend:
+            self._push_product_rows(0, self.n_psend_hub)                  # partial rows for rank 0 first ...
+            ev_p0 = cur.record_event()
+            with torch.cuda.stream(cs2):
+                cs2.wait_event(ev_p0)
+                self.exchange_partials(self._ppush_hub, last=False)       # ... and on their way at once
+            self._push_product_rows(self.n_psend_hub, self.n_psend)
+            ev_p = cur.record_event()
+            with torch.cuda.stream(cs2):
+                cs2.wait_event(ev_p)
+                self.exchange_partials(self._ppush_rest, last=True)
+                ev_y = cs2.record_event()
+        else:
+            self.push_product()
+            ev_p = cur.record_event()
+            with torch.cuda.stream(cs2):
+                cs2.wait_event(ev_p)
+                self.exchange_partials()
+                ev_y = cs2.record_event()
+        if self.split_pull:
+            cur.wait_event(ev_early)
+            self.pull_early.spmm(self.xbuf, out=self.y)                   # own columns + rows of ranks 1..s-1
+            cur.wait_event(ev_late)
+            cur.wait_event(ev_y)
+            if self.final is not None:
+                self.final.spmm(self._buf_all, e1=self.y, out=self.y)     # rank 0's rows + the partial rows, one pass
+            else:
+                self.pull_late.spmm(self.xbuf, e1=self.y, out=self.y)
+            return self.y
         if self.x_recv.shape[0]:
-            cur.wait_event(ev_x)                                          # rank 0 pulls nothing: no wait
+            cur.wait_event(ev_late)
         self.pull.spmm(self.xbuf, out=self.y)
+        if ev_late is not None:
+            # order the caller's next write into x_own after the exchange that READS it (rank 0 pulls nothing, yet
+            # its rows are still being pushed while its pull product runs); off the critical path here
+            cur.wait_event(ev_late)
         cur.wait_event(ev_y)
         if self.n_precv:
             self.add.spmm(self.precv, e1=self.y, out=self.y)              # fixed (row, source rank) order
-        return self.y
-
-
-class NvlsLShapedSpMM:
-    """L-shaped partition whose lowest `n_hubs` ranks ("hub ranks": on a skewed graph their rows/columns are the
-    ones everybody references) exchange through NVSwitch multicast instead of unicast rows:
-
-      X rows of a hub rank    one multimem.st broadcast of its whole block into the same symmetric region on every
-                              GPU (gdr_mc_broadcast_f32): the block leaves the hub once, the switch fans it out;
-                              every pull matrix addresses hub columns directly in that replica.
-      partial rows FOR a hub  every higher rank writes the dense product of its block (hub rows x own columns) into
-                              the same symmetric region locally; the hub adds all of them with ONE multimem.ld_reduce
-                              pass (gdr_mc_reduce_add_f32): the sum is formed in the switch, the hub receives each
-                              of its rows once instead of once per sender.
-    Non-hub traffic stays unicast peer stores (gdr_push_rows_f32) exactly as in LShapedSpMM(transport="p2p").
-    Measured motivation (R-MAT scale 24, p = 8): rank 0 owns 1.72 M rows but has to send 5.58 M row copies and
-    receive 5.58 M partial rows, 2-3x any other rank - its NVLink port is the step's critical path.
-
-    Symmetric buffer, same row offsets on every rank:
-      [HUBP Hrows | PSEND psend_max | HUBX Hrows | XOWN own_max | XRECV xrecv_max | PRECV precv_max]
-    push output = [HUBP | PSEND) (contiguous), pull input V = [HUBX .. PRECV) (column ids are V-relative)."""
-
-    def __init__(self, local_csr, bounds, rank, world, d, n_hubs=1, group=None, push_ctas=0):
-        import ctypes
-        import torch.distributed._symmetric_memory as symm
-        self.bounds = [int(b) for b in bounds]
-        self.rank, self.world, self.d, self.group = rank, world, d, group
-        nh = self.n_hubs = max(1, min(int(n_hubs), world - 1))
-        self.push_ctas = int(push_ctas)
-        dev = local_csr.device
-        s = rank
-        lo, hi = self.bounds[s], self.bounds[s + 1]
-        self.n, self.n_own = self.bounds[-1], hi - lo
-        self.is_hub = s < nh
-        bnd = torch.tensor(self.bounds, dtype=torch.int64, device=dev)
-        own_rows = [self.bounds[r + 1] - self.bounds[r] for r in range(world)]
-        hub_off = [sum(own_rows[:h]) for h in range(nh)]                  # row offset of hub h inside HUBX / HUBP
-        Hrows = sum(own_rows[:nh])
-        hub_off_t = torch.tensor(hub_off + [0] * (world - nh), dtype=torch.int64, device=dev)
-        col = local_csr.col.to(torch.int64)
-        deg = (local_csr.rowptr[1:] - local_csr.rowptr[:-1]).to(torch.int64)
-        row = torch.repeat_interleave(torch.arange(self.n_own, device=dev), deg)
-        owner = torch.searchsorted(bnd, col, right=True) - 1
-        val = local_csr.val
-
-        # ---- pull part (columns owned by ranks <= s): which rows still travel unicast ---------------------
-        keep = owner <= s
-        kcol, krow, kval, kown = col[keep], row[keep], val[keep], owner[keep]
-        k_hub = kown < nh
-        k_self = (kown == s) & ~k_hub
-        k_rem = ~k_hub & ~k_self
-        remote = torch.unique(kcol[k_rem])                                # sorted => grouped by (non-hub) owner
-        cut = torch.searchsorted(remote, bnd)
-        need_from = [remote[int(cut[r]):int(cut[r + 1])] - self.bounds[r] for r in range(world)]
-        self.xrecv_splits = [int(t.numel()) for t in need_from]
-        n_xrecv = int(sum(self.xrecv_splits))
-        want = torch.cat(need_from) if n_xrecv else torch.zeros(0, dtype=torch.int64, device=dev)
-        self.send_idx, self.xsend_splits = _a2a_var(want, self.xrecv_splits, group)
-
-        # ---- push part: entries above the diagonal go to their column owner, once --------------------------
-        up = ~keep
-        uo = owner[up]
-        order = torch.argsort(uo, stable=True)
-        cnt = torch.bincount(uo, minlength=world).tolist()
-        g_row, _ = _a2a_var((row[up] + lo)[order], cnt, group)
-        g_col, _ = _a2a_var(col[up][order], cnt, group)
-        g_val, _ = _a2a_var(val[up][order], cnt, group)                    # grouped by source rank, row-major inside
-        g_src = torch.searchsorted(bnd, g_row, right=True) - 1             # the row owner = the source rank
-        to_hub = g_src < nh
-        rows_u, inv = torch.unique(g_row[~to_hub], return_inverse=True)    # compact rows for non-hub owners
-        self.n_psend = int(rows_u.numel())
-        prow = torch.empty_like(g_row)
-        prow[to_hub] = hub_off_t[g_src[to_hub]] + (g_row[to_hub] - bnd[g_src[to_hub]])   # dense inside HUBP
-        prow[~to_hub] = Hrows + inv
-        self.push = csr_from_sorted_rows(prow, g_col - lo, g_val, Hrows + self.n_psend, self.n_own)
-        cut = torch.searchsorted(rows_u, bnd)
-        self.psend_splits = [int(cut[a + 1] - cut[a]) for a in range(world)]
-        back = rows_u - bnd[torch.searchsorted(bnd, rows_u, right=True) - 1]
-        add_rows, self.precv_splits = _a2a_var(back, self.psend_splits, group)
-        self.n_precv = int(add_rows.numel())
-        pos = torch.arange(self.n_precv, device=dev)
-        o2 = torch.argsort(add_rows, stable=True)
-        self.add = csr_from_sorted_rows(add_rows[o2], pos[o2], torch.ones(self.n_precv, dtype=val.dtype, device=dev),
-                                        self.n_own, max(self.n_precv, 1))
-
-        # ---- the symmetric buffer -----------------------------------------------------------------------------
-        meta = [None] * world
-        dist.all_gather_object(meta, dict(xrecv=self.xrecv_splits, precv=self.precv_splits, psend=self.n_psend),
-                               group=group)
-        psend_max = max(max(m["psend"] for m in meta), 1)
-        own_max = max(own_rows[nh:]) if world > nh else 1
-        xrecv_max = max(max(sum(m["xrecv"]) for m in meta), 1)
-        precv_max = max(max(sum(m["precv"]) for m in meta), 1)
-        A0 = 0
-        B0 = A0 + Hrows
-        C0 = B0 + psend_max
-        D0 = C0 + Hrows
-        E0 = D0 + own_max
-        F0 = E0 + xrecv_max
-        total = F0 + precv_max
-        self._symm_t = symm.empty(total * d, dtype=val.dtype, device=dev)
-        self._hdl = symm.rendezvous(self._symm_t, (group or dist.group.WORLD).group_name)
-        mc = int(getattr(self._hdl, "multicast_ptr", 0) or 0)
-        if mc == 0:
-            raise RuntimeError("NvlsLShapedSpMM: this system exposes no NVSwitch multicast mapping (NVLS)")
-        self._symm_t.zero_()                                               # HUBP regions nobody writes must read as 0
-        buf = self._symm_t.view(total, d)
-        esz = self._symm_t.element_size()
-        rowb = d * esz
-        self.push_out = buf[A0:A0 + Hrows + self.n_psend]
-        self.psend = buf[B0:B0 + self.n_psend]
-        self.xbuf = buf[C0:F0]                                             # V: what the pull matrix gathers from
-        self.x_own = buf[C0 + hub_off[s]:C0 + hub_off[s] + self.n_own] if self.is_hub else buf[D0:D0 + self.n_own]
-        self.x_recv = buf[E0:E0 + n_xrecv]
-        self.precv = buf[F0:F0 + self.n_precv]
-        self.y = torch.empty(self.n_own, d, dtype=val.dtype, device=dev)
-        self._mc_hubx = mc + (C0 + (hub_off[s] if self.is_hub else 0)) * rowb
-        self._mc_hubp = mc + (A0 + (hub_off[s] if self.is_hub else 0)) * rowb
-
-        # pull matrix with V-relative columns
-        new_col = torch.empty_like(kcol)
-        new_col[k_hub] = hub_off_t[kown[k_hub]] + (kcol[k_hub] - bnd[kown[k_hub]])
-        new_col[k_self] = (D0 - C0) + (kcol[k_self] - lo)
-        new_col[k_rem] = (E0 - C0) + torch.searchsorted(remote, kcol[k_rem])
-        self.pull = csr_from_sorted_rows(krow, new_col, kval, self.n_own, F0 - C0)
-        self.needs_remote_x = bool((k_rem.any() | (k_hub & (kown != s)).any()).item())
-
-        # unicast destination tables
-        base = [int(p) for p in self._hdl.buffer_ptrs]
-        arr, i64 = ctypes.c_void_p * world, ctypes.c_int64 * world
-        xdst, xidx, xcnt, off = [None] * world, [None] * world, [0] * world, 0
-        for r in range(world):
-            c = self.xsend_splits[r]
-            if c:
-                xdst[r] = base[r] + (E0 + sum(meta[r]["xrecv"][:s])) * rowb
-                xidx[r] = self.send_idx.data_ptr() + off * 8
-                xcnt[r] = c
-            off += c
-        self._xpush = (arr(*xdst), arr(*xidx), i64(*([0] * world)), i64(*xcnt))
-        pdst, pcnt, poff, off = [None] * world, [0] * world, [0] * world, 0
-        for a in range(world):
-            c = self.psend_splits[a]
-            if c:
-                pdst[a] = base[a] + (F0 + sum(meta[a]["precv"][:s])) * rowb
-                poff[a], pcnt[a] = off, c
-            off += c
-        self._ppush = (arr(*pdst), arr(*([None] * world)), i64(*poff), i64(*pcnt))
-
-        self.recv_rows = n_xrecv + self.n_precv + (0 if self.is_hub else Hrows)
-        self.comm_stream = torch.cuda.Stream(device=dev, priority=-1)
-        self.comm_stream2 = torch.cuda.Stream(device=dev, priority=-1)
-        self.transport = ("NVSwitch multicast for the %d hub rank(s) (multimem.st broadcast of their X block, "
-                          "multimem.ld_reduce of their partial rows) + p2p stores into peer symmetric memory for the "
-                          "rest, L-shaped partition" % nh)
-        torch.cuda.synchronize()
-        self._hdl.barrier(channel=3)                                       # everyone's zero fill is done
-        torch.cuda.synchronize()
-
-    @classmethod
-    def from_full(cls, full_csr, bounds, rank, world, d, **kw):
-        lo, hi = int(bounds[rank]), int(bounds[rank + 1])
-        p0, p1 = int(full_csr.rowptr[lo].item()), int(full_csr.rowptr[hi].item())
-        local = DeviceCSR((full_csr.rowptr[lo:hi + 1] - p0).contiguous(), full_csr.col[p0:p1].clone(),
-                          full_csr.val[p0:p1].clone(), hi - lo, full_csr.n_cols)
-        return cls(local, bounds, rank, world, d, **kw)
-
-    def _push(self, src, table):
-        dst, idx, off, cnt = table
-        _ffi.check(_ffi.lib().gdr_push_rows_f32(_ffi.ptr(src) if src.numel() else None, self.d, self.world, dst, idx,
-                                                off, cnt, self.push_ctas, _ffi.stream()), "push_rows")
-
-    def exchange_x(self):
-        self._hdl.barrier(channel=0)                 # every rank is done with last step's buffers
-        self._ev_b0 = torch.cuda.current_stream().record_event()
-        if self.is_hub:
-            _ffi.check(_ffi.lib().gdr_mc_broadcast_f32(_ffi.ptr(self.x_own), self._mc_hubx, self.n_own * self.d,
-                                                       self.push_ctas, _ffi.stream()), "mc_broadcast")
-        elif self.send_idx.numel():
-            self._push(self.x_own, self._xpush)
-        self._hdl.barrier(channel=1)                 # every replica and every pushed row has landed
-
-    def push_product(self):
-        if self.push.nnz:
-            self.push.spmm(self.x_own, out=self.push_out)      # dense hub partials | compact rows for the others
-
-    def exchange_partials(self):
-        torch.cuda.current_stream().wait_event(self._ev_b0)
-        if self.n_psend:
-            self._push(self.psend, self._ppush)
-        self._hdl.barrier(channel=2)                 # all partial rows are in place (HUBP locally, PRECV remotely)
-
-    def hub_reduce(self):
-        if self.is_hub:
-            _ffi.check(_ffi.lib().gdr_mc_reduce_add_f32(_ffi.ptr(self.y), self._mc_hubp, self.n_own * self.d, 0,
-                                                        _ffi.stream()), "mc_reduce_add")
-
-    def spmm(self, x_local=None):
-        if x_local is not None and x_local.data_ptr() != self.x_own.data_ptr():
-            self.x_own.copy_(x_local)
-        cur = torch.cuda.current_stream()
-        cs, cs2 = self.comm_stream, self.comm_stream2
-        cs.wait_stream(cur)
-        with torch.cuda.stream(cs):
-            self.exchange_x()
-            ev_x = cs.record_event()
-        cur.wait_event(self._ev_b0)                  # HUBP / PSEND of the previous step were consumed everywhere
-        self.push_product()
-        ev_p = cur.record_event()
-        with torch.cuda.stream(cs2):
-            cs2.wait_event(ev_p)
-            self.exchange_partials()
-            ev_y = cs2.record_event()
-        if self.needs_remote_x:
-            cur.wait_event(ev_x)
-        self.pull.spmm(self.xbuf, out=self.y)
-        cur.wait_event(ev_y)
-        if self.n_precv:
-            self.add.spmm(self.precv, e1=self.y, out=self.y)
-        self.hub_reduce()
         return self.y
 
 

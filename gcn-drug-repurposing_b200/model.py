@@ -28,6 +28,14 @@ from .graph import device_csr_of
 # Both are CUDA; this is a kernel choice, not a fallback.  Override with GDR_GEMM=simt|tc.
 GEMM_BACKEND = os.environ.get("GDR_GEMM", "tc")
 
+# The first layer's two aggregations P¹ = Â·X and T¹ = Â·(P¹ ⊙ X) (modules/model.py:163,168-169) depend only on the
+# input features and the adjacency, not on the weights (SURVEY §3.1 "hoistable").  When the SAME feature tensor
+# object (unchanged: same _version) meets the same adjacency again they are reused instead of recomputed — the way
+# the CSR conversion of the adjacency is reused.  train.py:159 builds a new device tensor every iteration
+# (`features.cuda()`), which never hits; a resident-features loop (trainer.GCNTrainer) hits from the 2nd iteration on.
+# GDR_HOIST=0 disables it.
+HOIST_LAYER1 = os.environ.get("GDR_HOIST", "1") != "0"
+
 
 # --------------------------------------------------------------------------------------------
 # raw-tensor building blocks (no autograd)
@@ -60,15 +68,28 @@ def _check_layer_shapes(x, w1, b1, w2, b2, csr):
             raise RuntimeError(f"{nm} must be an fp32 CUDA tensor (call model.cuda(); there is no CPU path)")
 
 
-def layer_forward_raw(csr, x, w1, b1, w2, b2, residual, decay):
+def _aggregate(csr, x, hoist_key=None):
+    """P = Â·x and T = Â·(P ⊙ x).  hoist_key: the caller's feature tensor OBJECT when these are the first layer's
+    aggregations; a strong reference is kept so that its storage cannot be recycled under the same address."""
+    if hoist_key is not None and HOIST_LAYER1:
+        c = getattr(csr, "_layer1_cache", None)
+        if (c is not None and c[0]._cdata == hoist_key._cdata and c[1] == hoist_key._version
+                and c[2] == tuple(x.shape)):      # same TensorImpl (kept alive by c[0]), never written since
+            return c[3], c[4]
+    p, px = csr.spmm(x, out2_mul=x)      # model.py:163, and torch.mul(P, X) of :168 from the same launch
+    t = csr.spmm(px)                     # model.py:169
+    if hoist_key is not None and HOIST_LAYER1:
+        csr._layer1_cache = (hoist_key, hoist_key._version, tuple(x.shape), p, t)
+    return p, t
+
+
+def layer_forward_raw(csr, x, w1, b1, w2, b2, residual, decay, hoist_key=None):
     """One GSS_GNNLayer application (+ the residual update of the network loop).
     Returns P = Â·x, T = Â·(P⊙x), Z (pre-nonlinearity), Xnext (= ELU(Z) or residual + decay*ELU(Z))."""
     L = _ffi.lib()
     _check_layer_shapes(x, w1, b1, w2, b2, csr)
     n, d = x.shape
-    p, px = csr.spmm(x, out2_mul=x)      # model.py:163, and torch.mul(P, X) of :168 from the same launch
-    t = csr.spmm(px)                     # model.py:169
-    del px
+    p, t = _aggregate(csr, x, hoist_key)
     z = torch.empty_like(x)
     xnext = torch.empty_like(x)
     if GEMM_BACKEND == "tc":
@@ -178,8 +199,10 @@ class _ResGCNFunction(torch.autograd.Function):
         xs, ps, ts, zs = [], [], [], []
         residual = None
         cur = x
-        for _ in range(num_layers):
-            p, t, z, xnext = layer_forward_raw(csr, cur, w1c, b1c, w2c, b2c, residual, decay)
+        for li in range(num_layers):
+            # layer 1 aggregates the caller's features: reusable while that tensor object is unchanged
+            key = x_in if (li == 0 and x is x_in and not x_in.requires_grad) else None
+            p, t, z, xnext = layer_forward_raw(csr, cur, w1c, b1c, w2c, b2c, residual, decay, hoist_key=key)
             xs.append(cur), ps.append(p), ts.append(t), zs.append(z)
             residual = z
             cur = xnext

@@ -1,0 +1,124 @@
+"""Multi-GPU sweep of the L-shaped partitioned SpMM (BASELINE configs[4]) over partition / schedule options in ONE
+launch: the R-MAT graph, the 1-GPU product and its timing are built once per rank, then every configuration is
+constructed, checked against the 1-GPU product on every rank, timed (max over ranks) and, with --diag, decomposed.
+
+    torchrun --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29500 profiles/sweep_lshape.py \
+        --configs "rw=6;rw=14;rw=14,hf=1;rw=14,hf=1,sp=1" [--scale 24] [--steps 10] [--diag]
+
+One JSON line per configuration on stdout (rank 0); E(p) = T(1) / (p T(p)) from the same process."""
+import argparse
+import datetime
+import json
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+import bench  # noqa: E402
+import gdr_b200 as gdr  # noqa: E402
+from gdr_b200 import dist as gdist  # noqa: E402
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--configs", default="rw=6;rw=14;rw=14,hf=1;rw=14,hf=1,sp=1")
+    ap.add_argument("--scale", type=int, default=24)
+    ap.add_argument("--d", type=int, default=128)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--diag", action="store_true")
+    args = ap.parse_args()
+    rank, world = int(os.environ["RANK"]), int(os.environ["WORLD_SIZE"])
+    dev = torch.device("cuda", int(os.environ.get("LOCAL_RANK", rank)))
+    torch.cuda.set_device(dev)
+    opts = dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)
+    dist.init_process_group("nccl", device_id=dev, pg_options=opts, timeout=datetime.timedelta(seconds=300))
+    full = bench.build_rmat_csr(args.scale, 32, dev)
+    n, d = full.n_rows, args.d
+    deg = (full.rowptr[1:] - full.rowptr[:-1]).to(torch.int64)
+    row_of = torch.repeat_interleave(torch.arange(n, device=dev), deg)
+    hist, bin_size = gdist.coarse_histogram(row_of, full.col.to(torch.int64), n, min(1024, n))
+    del row_of, deg
+    hist_np = hist.cpu().numpy()
+    x_full = torch.randn(n, d, device=dev, generator=torch.Generator(device=dev).manual_seed(2))
+    y_full = full.spmm(x_full)
+    a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    a.record()
+    for _ in range(3):
+        full.spmm(x_full, out=y_full)
+    b.record()
+    torch.cuda.synchronize()
+    ms1 = a.elapsed_time(b) / 3
+
+    def timed(fn, reps):
+        torch.cuda.synchronize()
+        dist.barrier()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        t = torch.tensor([e0.elapsed_time(e1) / reps], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item()), e0.elapsed_time(e1) / reps
+
+    for spec in [c for c in args.configs.split(";") if c.strip()]:
+        kv = dict(item.split("=") for item in spec.split(","))
+        rw, cw = float(kv.get("rw", 6)), float(kv.get("cw", 0))
+        hf, sp, ctas = bool(int(kv.get("hf", 0))), bool(int(kv.get("sp", 0))), int(kv.get("ctas", 0))
+        bounds = gdist.lshape_bounds(hist_np, bin_size, n, world, row_weight=rw, comm_weight=cw)
+        lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+        part = gdist.LShapedSpMM.from_full(full, bounds, rank, world, d, transport="p2p", push_ctas=ctas,
+                                           hub_first=hf, split_pull=sp)
+        part.x_own.copy_(x_full[lo:hi])
+        y = part.spmm(None)
+        ref = y_full[lo:hi]
+        err = (y - ref).abs()
+        strict = (err <= 1e-6) | (err <= 1e-5 * ref.abs())
+        ok = bool((strict | (err <= 4e-7 * ref.abs().max())).all().item())
+        chk = torch.tensor([float(strict.double().mean().item()), float(ok)], device=dev, dtype=torch.float64)
+        dist.all_reduce(chk, op=dist.ReduceOp.MIN)
+        del err, strict
+        for _ in range(args.warmup):
+            part.spmm(None)
+        ms, _ = timed(lambda: part.spmm(None), args.steps)
+        if args.diag:
+            nop = lambda: None  # noqa: E731
+            _, t_x = timed(part.exchange_x, 5)
+            _, t_push = timed(part.push_product, 5)
+            _, t_p = timed(part.exchange_partials, 5)
+            _, t_pull = timed(lambda: part.pull.spmm(part.xbuf, out=part.y), 5)
+            _, t_add = timed((lambda: part.add.spmm(part.precv, e1=part.y, out=part.y)) if part.n_precv else nop, 5)
+            t_early = t_final = 0.0
+            if part.split_pull:
+                _, t_early = timed(lambda: part.pull_early.spmm(part.xbuf, out=part.y), 5)
+                _, t_final = timed((lambda: part.final.spmm(part._buf_all, e1=part.y, out=part.y))
+                                   if part.final is not None else nop, 5)
+            else:
+                timed(nop, 1), timed(nop, 1)
+            sys.stderr.write("[diag %s] rank %d rows %d | x-exch %.2f (recv %d send %d) | push %.2f (nnz %d, %d rows, hub "
+                             "%d) | p-exch %.2f (recv %d) | pull %.2f (nnz %d) | add %.2f | early %.2f final %.2f\n" % (
+                                 spec, rank, hi - lo, t_x, sum(part.xrecv_splits), int(part.send_idx.numel()), t_push,
+                                 part.push.nnz, part.n_psend, part.n_psend_hub, t_p, part.n_precv, t_pull,
+                                 part.pull.nnz, t_add, t_early, t_final))
+            sys.stderr.flush()
+        if rank == 0:
+            print(json.dumps({"config": spec, "n_gpus": world, "scale": args.scale, "d": d, "ms_per_step": ms,
+                              "same_product_on_1_gpu_ms": ms1, "efficiency_vs_1gpu": ms1 / (world * ms),
+                              "gedges_per_s": full.nnz / (ms * 1e-3) / 1e9, "bounds": [int(v) for v in bounds],
+                              "strict_fraction_worst_rank": float(chk[0].item()),
+                              "within_tolerance_all_ranks": bool(chk[1].item() > 0.5)}), flush=True)
+        del part, y
+        torch.cuda.empty_cache()
+        dist.barrier()
+    dist.destroy_process_group()
+
+
+if __name__ == "__main__":
+    main()
