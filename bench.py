@@ -87,7 +87,7 @@ def parse_args():
     p.add_argument("--row-weight", type=float, default=DIST_ROW_WEIGHT,
                    help="partition balance: cost(row) = nnz(row) + row_weight, the per-row overhead of the SpMM kernel in "
                         "edge-equivalents (DESIGN.md, multi-GPU)")
-    p.add_argument("--cpu-iters", type=int, default=8, help="iterations of the CPU baseline sample (median reported)")
+    p.add_argument("--cpu-iters", type=int, default=24, help="iterations of the CPU baseline sample (median reported)")
     return p.parse_args()
 
 

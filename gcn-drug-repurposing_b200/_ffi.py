@@ -93,6 +93,9 @@ _SIGNATURES = {
     "gdr_rank_embedding_f64": (c_i32, [c_ptr, c_i64, c_i64, c_i32, c_i64, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr,
                                        c_i64, c_ptr]),
     "gdr_rank_values_f64": (c_i32, [c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_ptr]),
+    "gdr_text_format_edgelist": (c_i64, [ctypes.c_char_p, c_ptr, c_ptr, c_i64, c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_i64,
+                                         c_i32]),
+    "gdr_text_parse_edgelist": (c_i64, [ctypes.c_char_p, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_i32]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

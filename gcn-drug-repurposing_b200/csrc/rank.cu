@@ -93,13 +93,13 @@ int64_t gdr_rank_workspace_bytes(int64_t m) {
 int gdr_rank_embedding_f64(const double *embs, int64_t n, int64_t d, int normalize, int64_t query_row,
                            const int32_t *sel, int64_t m, double *prox_out, int32_t *order_out, double *sorted_out,
                            void *workspace, int64_t workspace_bytes, gdr_stream_t stream) {
-  GDR_CHECK_ARG(n > 0 && d > 0 && m >= 0 && embs && prox_out && order_out && workspace, GDR_E_BADARG,
-                "rank_embedding: bad args");
+  GDR_CHECK_ARG(n > 0 && d > 0 && m >= 0, GDR_E_BADARG, "rank_embedding: bad sizes");
+  if (m == 0) return GDR_OK;
+  GDR_CHECK_ARG(embs && prox_out && order_out && workspace, GDR_E_BADARG, "rank_embedding: null pointer");
   GDR_CHECK_ARG(query_row >= 0 && query_row < n, GDR_E_BADARG, "rank_embedding: query row %lld outside [0, %lld)",
                 (long long)query_row, (long long)n);
   GDR_CHECK_ARG(m < (int64_t)INT32_MAX, GDR_E_SHAPE, "rank_embedding: int32 index range exceeded");
   GDR_CHECK_ARG(workspace_bytes >= gdr_rank_workspace_bytes(m), GDR_E_WORKSPACE, "rank_embedding: workspace too small");
-  if (m == 0) return GDR_OK;
   cudaStream_t st = as_stream(stream);
   Carver cv(workspace);
   double *sorted = cv.take<double>(m);
@@ -113,10 +113,11 @@ int gdr_rank_embedding_f64(const double *embs, int64_t n, int64_t d, int normali
 // consumer (predict_drug.py:111-124: rank the drug entries of the NodeCovid profile).
 int gdr_rank_values_f64(const double *values, const int32_t *sel, int64_t m, double *values_out, int32_t *order_out,
                         double *sorted_out, void *workspace, int64_t workspace_bytes, gdr_stream_t stream) {
-  GDR_CHECK_ARG(m >= 0 && values && values_out && order_out && workspace, GDR_E_BADARG, "rank_values: bad args");
+  GDR_CHECK_ARG(m >= 0, GDR_E_BADARG, "rank_values: bad size");
+  if (m == 0) return GDR_OK;
+  GDR_CHECK_ARG(values && values_out && order_out && workspace, GDR_E_BADARG, "rank_values: null pointer");
   GDR_CHECK_ARG(m < (int64_t)INT32_MAX, GDR_E_SHAPE, "rank_values: int32 index range exceeded");
   GDR_CHECK_ARG(workspace_bytes >= gdr_rank_workspace_bytes(m), GDR_E_WORKSPACE, "rank_values: workspace too small");
-  if (m == 0) return GDR_OK;
   cudaStream_t st = as_stream(stream);
   Carver cv(workspace);
   double *sorted = cv.take<double>(m);

@@ -4,10 +4,14 @@
 //     value widened to double — reproduced byte for byte, rows formatted in parallel.
 //   * node2vec's .embs.txt as train.py:79-80 reads it (header line skipped, first column = node name, the rest
 //     parsed by float() = correctly rounded strtod), lines parsed in parallel.
+//   * whole_graph.weighted.edgelist as nx.write_weighted_edgelist writes it (predict_drug.py:225-226,
+//     run_covid.py:150-151): one line "u v w" per edge with w = str(float) = Python's repr, i.e. the shortest
+//     digit string that round-trips, in fixed notation for decimal exponents in [-4, 16), else 'd.ddde+XX'.
 #include <math.h>
 #include <stdlib.h>
 #include <string.h>
 
+#include <charconv>
 #include <string>
 #include <thread>
 #include <vector>
@@ -63,11 +67,166 @@ static int64_t format_all(const T *x, int64_t n, int64_t d, char *out, int64_t c
   return total;
 }
 
+// Python's repr(float) (float_repr_style 'short'): shortest round-trip digits (std::to_chars yields the same digit
+// string: both are exact shortest-representation algorithms), laid out by PyOS_double_to_string's 'r' rule.
+static int fmt_py_repr(char *dst, double v) {
+  if (isnan(v)) { memcpy(dst, "nan", 3); return 3; }
+  if (isinf(v)) { const int k = v < 0 ? 4 : 3; memcpy(dst, v < 0 ? "-inf" : "inf", (size_t)k); return k; }
+  char sci[40];
+  auto r = std::to_chars(sci, sci + sizeof(sci) - 1, v, std::chars_format::scientific);  // [-]d[.ddd]e[+-]XX
+  *r.ptr = 0;
+  const char *p = sci, *e = r.ptr;
+  char *o = dst;
+  if (*p == '-') *o++ = *p++;
+  char digits[24];
+  int nd = 0;
+  const char *q = p;
+  for (; q < e && *q != 'e'; ++q)
+    if (*q != '.') digits[nd++] = *q;
+  const int exp10 = atoi(q + 1);           // value = d.ddd x 10^exp10
+  const int decpt = exp10 + 1;             // digits to the left of the decimal point
+  if (decpt > 16 || decpt < -3) {          // exponent form: d[.ddd]e[+-]XX (at least two exponent digits)
+    *o++ = digits[0];
+    if (nd > 1) {
+      *o++ = '.';
+      memcpy(o, digits + 1, (size_t)(nd - 1));
+      o += nd - 1;
+    }
+    o += snprintf(o, 8, "e%c%02d", exp10 < 0 ? '-' : '+', exp10 < 0 ? -exp10 : exp10);
+  } else if (decpt <= 0) {                 // 0.000ddd
+    *o++ = '0';
+    *o++ = '.';
+    for (int i = 0; i < -decpt; ++i) *o++ = '0';
+    memcpy(o, digits, (size_t)nd);
+    o += nd;
+  } else if (decpt >= nd) {                // ddd000.0
+    memcpy(o, digits, (size_t)nd);
+    o += nd;
+    for (int i = nd; i < decpt; ++i) *o++ = '0';
+    *o++ = '.';
+    *o++ = '0';
+  } else {                                 // dd.ddd
+    memcpy(o, digits, (size_t)decpt);
+    o += decpt;
+    *o++ = '.';
+    memcpy(o, digits + decpt, (size_t)(nd - decpt));
+    o += nd - decpt;
+  }
+  return (int)(o - dst);
+}
+
+static int clamp_threads(int n_threads, int64_t work) {
+  if (n_threads <= 0) n_threads = (int)std::thread::hardware_concurrency();
+  if (n_threads < 1) n_threads = 1;
+  if (n_threads > 64) n_threads = 64;
+  if ((int64_t)n_threads > work) n_threads = (int)(work > 0 ? work : 1);
+  return n_threads;
+}
+
 }  // namespace gdr
 
 using namespace gdr;
 
 extern "C" {
+
+// "<name[src]> <name[dst]> <repr(w)>\n" per edge, as nx.write_weighted_edgelist (predict_drug.py:225-226).
+// names: one blob + per-node (offset, length).  Returns bytes written, -needed if out_cap is too small (call with
+// out == NULL / out_cap == 0 to size the buffer), or a negative GDR_E_* code.
+int64_t gdr_text_format_edgelist(const char *names, const int64_t *name_off, const int32_t *name_len, int64_t n_nodes,
+                                 const int32_t *src, const int32_t *dst, const double *w, int64_t n_edges, char *out,
+                                 int64_t out_cap, int n_threads) {
+  GDR_CHECK_ARG(n_nodes >= 0 && n_edges >= 0 && (n_edges == 0 || (names && name_off && name_len && src && dst && w)),
+                GDR_E_BADARG, "text_format_edgelist: bad args");
+  const int nt = clamp_threads(n_threads, n_edges);
+  std::vector<std::string> parts((size_t)nt);
+  std::vector<int> bad((size_t)nt, 0);
+  std::vector<std::thread> th;
+  for (int t = 0; t < nt; ++t) {
+    th.emplace_back([&, t]() {
+      std::string &o = parts[(size_t)t];
+      char buf[48];
+      for (int64_t i = n_edges * t / nt; i < n_edges * (t + 1) / nt; ++i) {
+        if (src[i] < 0 || src[i] >= n_nodes || dst[i] < 0 || dst[i] >= n_nodes) { bad[(size_t)t] = 1; return; }
+        o.append(names + name_off[src[i]], (size_t)name_len[src[i]]);
+        o.push_back(' ');
+        o.append(names + name_off[dst[i]], (size_t)name_len[dst[i]]);
+        o.push_back(' ');
+        o.append(buf, (size_t)fmt_py_repr(buf, w[i]));
+        o.push_back('\n');
+      }
+    });
+  }
+  for (auto &t : th) t.join();
+  for (int b : bad) GDR_CHECK_ARG(!b, GDR_E_BADARG, "text_format_edgelist: node index out of range");
+  int64_t total = 0;
+  for (auto &p : parts) total += (int64_t)p.size();
+  if (!out || total > out_cap) return -total;
+  int64_t off = 0;
+  for (auto &p : parts) {
+    memcpy(out + off, p.data(), p.size());
+    off += (int64_t)p.size();
+  }
+  return total;
+}
+
+// nx.read_weighted_edgelist semantics (run_covid.py:150-151 reads what predict_drug.py:225-226 wrote): lines starting
+// with '#' and blank lines are skipped, "u v w" split on whitespace, w = float().  Pass 1 (w_out == NULL): returns
+// the number of edges.  Pass 2: byte spans of both names and the weight of every edge.  Negative code on a bad line.
+int64_t gdr_text_parse_edgelist(const char *text, int64_t len, int64_t *u_off, int32_t *u_len, int64_t *v_off,
+                                int32_t *v_len, double *w_out, int n_threads) {
+  GDR_CHECK_ARG(text && len >= 0, GDR_E_BADARG, "text_parse_edgelist: bad args");
+  auto is_sp = [](char c) { return c == ' ' || c == '\t' || c == '\r'; };
+  std::vector<int64_t> starts;
+  int64_t pos = 0;
+  while (pos < len) {
+    const char *nl = static_cast<const char *>(memchr(text + pos, '\n', (size_t)(len - pos)));
+    const int64_t end = nl ? (int64_t)(nl - text) : len;
+    int64_t i = pos;
+    while (i < end && is_sp(text[i])) ++i;
+    if (i < end && text[i] != '#') starts.push_back(i);
+    pos = end + 1;
+  }
+  const int64_t n = (int64_t)starts.size();
+  if (!w_out) return n;
+  GDR_CHECK_ARG(u_off && u_len && v_off && v_len, GDR_E_BADARG, "text_parse_edgelist: missing outputs");
+  const int nt = clamp_threads(n_threads, n);
+  std::vector<int> bad((size_t)nt, 0);
+  std::vector<std::thread> th;
+  for (int t = 0; t < nt; ++t) {
+    th.emplace_back([&, t]() {
+      std::string tok;
+      for (int64_t i = n * t / nt; i < n * (t + 1) / nt; ++i) {
+        int64_t p = starts[(size_t)i];
+        const char *nl = static_cast<const char *>(memchr(text + p, '\n', (size_t)(len - p)));
+        const int64_t e = nl ? (int64_t)(nl - text) : len;
+        int64_t span[3][2];
+        int k = 0;
+        while (p < e && k < 3) {
+          while (p < e && is_sp(text[p])) ++p;
+          if (p >= e) break;
+          span[k][0] = p;
+          while (p < e && !is_sp(text[p])) ++p;
+          span[k][1] = p;
+          ++k;
+        }
+        while (p < e && is_sp(text[p])) ++p;
+        if (k != 3 || p < e) { bad[(size_t)t] = 1; return; }      // networkx raises on a line without exactly 3 fields
+        u_off[i] = span[0][0]; u_len[i] = (int32_t)(span[0][1] - span[0][0]);
+        v_off[i] = span[1][0]; v_len[i] = (int32_t)(span[1][1] - span[1][0]);
+        tok.assign(text + span[2][0], (size_t)(span[2][1] - span[2][0]));
+        char *endp = nullptr;
+        w_out[i] = strtod(tok.c_str(), &endp);
+        if (endp != tok.c_str() + tok.size()) { bad[(size_t)t] = 2; return; }
+      }
+    });
+  }
+  for (auto &t : th) t.join();
+  for (int b : bad) {
+    GDR_CHECK_ARG(b != 1, GDR_E_SHAPE, "text_parse_edgelist: a line does not have exactly 3 fields");
+    GDR_CHECK_ARG(b != 2, GDR_E_BADARG, "text_parse_edgelist: a weight is not a number");
+  }
+  return n;
+}
 
 int64_t gdr_text_savetxt_bytes(int64_t n, int64_t d) { return (n < 0 || d < 0) ? GDR_E_BADARG : n * (d * 26 + 1) + 16; }
 

@@ -310,6 +310,17 @@ int64_t gdr_text_savetxt_e18(const void *x, int64_t n, int64_t d, int elem_bytes
 int64_t gdr_text_parse_embs(const char *text, int64_t len, int skip_rows, double *values, int64_t d,
                             int64_t *name_off, int32_t *name_len, int64_t *d_out, int n_threads);
 
+/* whole_graph.weighted.edgelist as nx.write_weighted_edgelist / nx.read_weighted_edgelist handle it
+ * (predict_drug.py:225-226, run_covid.py:150-151): one line "u v w" per edge, w = Python's repr(float).
+ * format: names = one blob + per-node (offset, length); returns bytes written, or -needed when out is NULL / too
+ * small.  parse: pass 1 (w_out == NULL) returns the edge count ('#' comments and blank lines skipped), pass 2 fills
+ * the byte spans of both node names and the weights.                                                             */
+int64_t gdr_text_format_edgelist(const char *names, const int64_t *name_off, const int32_t *name_len, int64_t n_nodes,
+                                 const int32_t *src, const int32_t *dst, const double *w, int64_t n_edges, char *out,
+                                 int64_t out_cap, int n_threads);
+int64_t gdr_text_parse_edgelist(const char *text, int64_t len, int64_t *u_off, int32_t *u_len, int64_t *v_off,
+                                int32_t *v_len, double *w_out, int n_threads);
+
 #ifdef __cplusplus
 }
 #endif

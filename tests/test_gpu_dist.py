@@ -25,7 +25,7 @@ def test_push_rows_local_destinations_match_index_select(gdr, d, counts, n_ctas)
     k = len(counts)
     idx = [torch.randint(0, n_src, (c,), device=dev, generator=g) if (i % 2 == 0) else None
            for i, c in enumerate(counts)]                               # odd destinations: contiguous ranges (idx NULL)
-    offs = [int(torch.randint(0, n_src - c, (1,)).item()) if c else 0 for c in counts]
+    offs = [int(torch.randint(0, n_src - c, (1,)).item()) if (c and idx[i] is None) else 0 for i, c in enumerate(counts)]
     dst = [torch.full((max(c, 1), d), float("nan"), device=dev) for c in counts]
     arr, i64 = ctypes.c_void_p * k, ctypes.c_int64 * k
     rc = L.gdr_push_rows_f32(src.data_ptr(), d, k, arr(*[t.data_ptr() for t in dst]),
