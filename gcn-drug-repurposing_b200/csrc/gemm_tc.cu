@@ -6,21 +6,23 @@
 // modules/model.py:163-173, 218-221) and parity is 1e-5 relative.  Each operand is therefore split as
 // x = hi + lo with hi = rn_tf32(x), lo = rn_tf32(x - hi) (split_tf32_kernel, exact residual), and the
 // product is evaluated as  hi·hi  +  (hi·lo + lo·hi)  — three TF32 MMAs per K step ("3xTF32").  The
-// dropped lo·lo term and the rounding of lo are both <= 2^-22 relative per term.  Tensor-core
-// accumulation may round toward zero, which biases long accumulation chains; two measures keep that
-// below the fp32 rounding noise of the reference itself:
-//   * the small correction products accumulate in their OWN TMEM accumulator (their rounding errors
-//     are 2^-11 smaller), and
-//   * the hi·hi chain is cut into up to TC_KCHUNKS accumulators over K; all of them are summed in
-//     round-to-nearest fp32 in the epilogue.
+// dropped lo·lo term and the rounding of lo are both <= 2^-22 relative per term.  The small correction
+// products accumulate in their OWN TMEM accumulator (their rounding errors are 2^-11 smaller) and are
+// added to the hi·hi accumulator in round-to-nearest fp32 in the epilogue.
 //
-// Structure (one 128 x 128 output tile per CTA, 192 threads):
-//   warp 0   TMA producer: four tiles per stage (A_hi, A_lo, B_hi, B_lo; 128 rows x 32 fp32 = 128-byte
-//            rows, SWIZZLE_128B) into a 3-stage ring, completion on `full` mbarriers
-//   warp 1   allocates 512 TMEM columns; one elected lane issues tcgen05.mma (kind::tf32, M=128, N=128,
-//            K=8) 12 times per stage and releases the stage with tcgen05.commit -> `empty` mbarrier
-//   warps 2-5 epilogue: tcgen05.ld (32 lanes x 32 columns per warp and step), sum of the accumulators,
-//            fused epilogue (bias / ELU / residual, GSS loss + dG, split-K partials, radix histogram)
+// Structure: persistent kernel, one CTA per SM walking 128 x 128 output tiles; see gemm_tc_kernel below.
+//   warp 0    TMA producer: four tiles per stage (A_hi, A_lo, B_hi, B_lo; 128 rows x 32 fp32 = 128-byte rows,
+//             SWIZZLE_128B) into a 3-stage ring, completion on `full` mbarriers
+//   warp 1    allocates 512 TMEM columns = two accumulator sets [hi·hi | corrections]; one elected lane issues
+//             tcgen05.mma (kind::tf32, M=128, N=128, K=8) 12 times per stage, releases the stage with
+//             tcgen05.commit -> `empty`, and the tile with tcgen05.commit -> `acc_full`
+//   warps 2-5 epilogue: tcgen05.ld (32 lanes x 32 columns), sum of the two accumulators, transposition through
+//             shared memory, fused epilogue (bias / ELU / residual, GSS loss + dG, split-K partials, radix
+//             histogram) with coalesced stores; overlaps the next tile's main loop (`acc_empty`)
+//   warps 6-9 (RAW_A) split the raw fp32 A tile into hi / lo in shared memory
+// Measured (tests/test_gpu_tc.py): one hi·hi accumulator per tile keeps the error at 4-6e-7 of sum|a||b|, the level
+// of torch-CPU / cuBLAS fp32 (2-5e-7); round 1 cut the chain into three accumulators (1.4-3.1e-7) but that used all
+// 512 TMEM columns for one tile and left the epilogue un-overlapped.
 #include <algorithm>
 
 #include "gemm_tc.cuh"
@@ -28,15 +30,17 @@
 
 namespace gdr {
 
-constexpr int TC_BM = 128, TC_BN = 128, TC_BK = 32, TC_STAGES = 3, TC_THREADS = 192;
-constexpr int TC_KCHUNKS = 3;                                 // hi·hi accumulators (+1 for the corrections)
+constexpr int TC_BM = 128, TC_BN = 128, TC_BK = 32, TC_STAGES = 3;
+constexpr int TC_THREADS = 192, TC_THREADS_RAW = 320;         // + 4 converter warps when A is split in the kernel
 constexpr int TC_TILE_BYTES = TC_BM * TC_BK * 4;              // 16 KB per operand tile
 constexpr int TC_STAGE_BYTES = 4 * TC_TILE_BYTES;             // A_hi, A_lo, B_hi, B_lo
-constexpr int TC_SMEM_BYTES = TC_STAGES * TC_STAGE_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
+constexpr int TC_STG_BYTES = 4 * 32 * 33 * 4;                 // per-warp 32 x 33 transposition buffers of the epilogue
+constexpr int TC_SMEM_BYTES = TC_STAGES * TC_STAGE_BYTES + TC_STG_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
 
 struct TcParams {
   int64_t m, n, k;         // k = full reduction length (all of it unless split-K)
-  int64_t k_per_split;     // EPI_SPLITK: K range of blockIdx.z (multiple of TC_BK); otherwise >= k
+  int64_t k_per_split;     // EPI_SPLITK: K range of one split (multiple of TC_BK); otherwise >= k
+  int64_t splits;          // EPI_SPLITK: number of K ranges (tiles = tiles_m * tiles_n * splits); otherwise 1
   int64_t k_a2;            // RAW_A: columns [k_a2, k) of A come from the second raw source (k_a2 % TC_BK == 0)
   GemmParams g;            // epilogue operands, same meaning as in gemm_simt.cuh (a/b/lda/ldb unused)
 };
@@ -92,105 +96,120 @@ split_tf32_transpose_kernel(const float *__restrict__ s, int64_t ld, int64_t row
   }
 }
 
-// ---- fused epilogues: one thread owns 32 consecutive columns [n, n+32) of output row m -----------------
+// ---- fused epilogues ---------------------------------------------------------------------------------------
+// After the TMEM read a thread owns 32 consecutive columns of ONE output row; stores in that layout would touch
+// 32 different rows per instruction.  Each epilogue warp therefore transposes its 32x32 block through a padded
+// shared-memory buffer and works on it as 8 steps of 4 rows x 32 columns: lane l owns columns 4*(l%8)..+3 of
+// row 4*i + l/8, so every global load / store of the warp covers 4 row segments of 128 contiguous bytes, and the
+// loads of all 8 steps (residual, addend, bias) are issued before any of them is consumed.
+constexpr int TC_STG_LD = 33;  // padded row length of the staging buffer (bank-conflict free both ways)
+
 template <int EPI>
-__device__ __forceinline__ void tc_epilogue_row(const TcParams &p, int64_t m, int64_t n, float (&v)[32], double &lsum,
-                                                unsigned int *sh_hist, unsigned int &best) {
+__device__ __forceinline__ void tc_epilogue_block(const TcParams &p, int64_t z, int64_t m_base, int64_t n_base,
+                                                  const float *__restrict__ stg, int lane, double &lsum) {
   const GemmParams &g = p.g;
-  if (EPI == EPI_HIST) {
-    const unsigned int prefix = g.sel->prefix, mask = g.sel->mask;
+  const int rq = lane >> 3, cq = (lane & 7) * 4;
+  const int64_t nn = n_base + cq;
+  const int64_t n_lim = (EPI == EPI_GSS) ? g.ldc : p.n;  // every other caller has n % 4 == 0
+  if (nn >= n_lim) return;
+  float4 add1[8], add2[8];
+  float4 bias = make_float4(0.f, 0.f, 0.f, 0.f);
+  if (EPI == EPI_LAYER) {
+    const float4 b1 = ldg_f4(g.bias1 + nn), b2 = ldg_f4(g.bias2 + nn);
+    bias = make_float4(b1.x + b2.x, b1.y + b2.y, b1.z + b2.z, b1.w + b2.w);
+  }
+  const bool has_add = (EPI == EPI_STORE && g.e1 != nullptr) || (EPI == EPI_LAYER && g.residual != nullptr);
+  if (has_add) {
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      if (n + j < p.n) {
-        const unsigned int key = f32_key(v[j]);
-        if ((key & mask) == prefix) atomicAdd(&sh_hist[(key >> g.shift) & g.bin_mask], 1u);
+    for (int i = 0; i < 8; ++i) {
+      const int64_t m = m_base + i * 4 + rq;
+      if (m < p.m) {
+        if (EPI == EPI_STORE) {
+          add1[i] = ldg_f4(g.e1 + m * g.ldc + nn);
+          add2[i] = ldg_f4(g.e2 + m * g.ldc + nn);
+        } else {
+          add1[i] = ldg_f4(g.residual + m * g.ldc + nn);
+        }
       }
     }
-    return;
   }
-  if (EPI == EPI_MINGT) {
-    const unsigned int base = g.sel->prefix;
 #pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      if (n + j < p.n) {
-        const unsigned int key = f32_key(v[j]);
-        if (key > base) best = min(best, key);
+  for (int i = 0; i < 8; ++i) {
+    const int r = i * 4 + rq;
+    const int64_t m = m_base + r;
+    if (m >= p.m) continue;
+    const float *sp = stg + r * TC_STG_LD + cq;
+    float a0 = sp[0], a1 = sp[1], a2 = sp[2], a3 = sp[3];
+    if (EPI == EPI_GSS) {
+      float v[4] = {a0, a1, a2, a3};
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        float w = 0.f;
+        if (nn + j < p.n) {
+          const float gv = v[j];
+          const float rr = fmaxf(gv, 0.f) - g.beta;
+          lsum += (double)(-0.5f * g.alpha * rr * rr);
+          w = gv > 0.f ? -g.alpha * rr * g.wscale : 0.f;
+        }
+        v[j] = w;
       }
+      a0 = v[0]; a1 = v[1]; a2 = v[2]; a3 = v[3];
     }
-    return;
-  }
-  if (EPI == EPI_GSS) {  // n need not be a multiple of 4; ldc is
-#pragma unroll
-    for (int j = 0; j < 32; ++j) {
-      float w = 0.f;
-      if (n + j < p.n) {
-        const float gv = v[j];
-        const float r = fmaxf(gv, 0.f) - g.beta;
-        lsum += (double)(-0.5f * g.alpha * r * r);
-        w = gv > 0.f ? -g.alpha * r * g.wscale : 0.f;
-      }
-      v[j] = w;
-    }
-  }
-  float *crow = g.c + (EPI == EPI_SPLITK ? ((int64_t)blockIdx.z * p.m + m) : m) * g.ldc + n;
-#pragma unroll
-  for (int q = 0; q < 8; ++q) {
-    const int64_t nn = n + q * 4;
-    if (nn >= (EPI == EPI_GSS ? g.ldc : p.n)) break;  // every other caller has n % 4 == 0
-    float a0 = v[q * 4 + 0], a1 = v[q * 4 + 1], a2 = v[q * 4 + 2], a3 = v[q * 4 + 3];
-    if (EPI == EPI_STORE && g.e1) {
-      const float4 x = ldg_f4(g.e1 + m * g.ldc + nn), y = ldg_f4(g.e2 + m * g.ldc + nn);
-      a0 = fmaf(x.x, y.x, a0); a1 = fmaf(x.y, y.y, a1); a2 = fmaf(x.z, y.z, a2); a3 = fmaf(x.w, y.w, a3);
+    if (EPI == EPI_STORE && has_add) {
+      a0 = fmaf(add1[i].x, add2[i].x, a0); a1 = fmaf(add1[i].y, add2[i].y, a1);
+      a2 = fmaf(add1[i].z, add2[i].z, a2); a3 = fmaf(add1[i].w, add2[i].w, a3);
     }
     if (EPI == EPI_LAYER) {
-      const float4 b1 = ldg_f4(g.bias1 + nn), b2 = ldg_f4(g.bias2 + nn);
-      a0 += b1.x + b2.x; a1 += b1.y + b2.y; a2 += b1.z + b2.z; a3 += b1.w + b2.w;
+      a0 += bias.x; a1 += bias.y; a2 += bias.z; a3 += bias.w;
     }
-    *reinterpret_cast<float4 *>(crow + q * 4) = make_float4(a0, a1, a2, a3);
+    float *crow = g.c + (EPI == EPI_SPLITK ? (z * p.m + m) : m) * g.ldc + nn;
+    *reinterpret_cast<float4 *>(crow) = make_float4(a0, a1, a2, a3);
     if (EPI == EPI_LAYER) {
       float y0 = elu1(a0), y1 = elu1(a1), y2 = elu1(a2), y3 = elu1(a3);
-      if (g.residual) {
-        const float4 r = ldg_f4(g.residual + m * g.ldc + nn);
-        y0 = fmaf(g.decay, y0, r.x); y1 = fmaf(g.decay, y1, r.y);
-        y2 = fmaf(g.decay, y2, r.z); y3 = fmaf(g.decay, y3, r.w);
+      if (has_add) {
+        y0 = fmaf(g.decay, y0, add1[i].x); y1 = fmaf(g.decay, y1, add1[i].y);
+        y2 = fmaf(g.decay, y2, add1[i].z); y3 = fmaf(g.decay, y3, add1[i].w);
       }
       *reinterpret_cast<float4 *>(g.xnext + m * g.ldc + nn) = make_float4(y0, y1, y2, y3);
     }
   }
 }
 
-// RAW_A: operand A arrives as plain fp32 (map_ahi = first source, map_alo = second source placed after it along
-// K) and is split into hi/lo in shared memory by the four epilogue warps while the pipeline runs: the TMA tile is
-// rewritten in place as hi, lo goes to the neighbouring slot, fence.proxy.async makes both visible to the
-// tensor core, and a `conv` mbarrier (128 arrivals) replaces `full` as the MMA issuer's go signal.
+__device__ __forceinline__ void named_bar_sync(int id, int threads) {
+  asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(threads) : "memory");
+}
+
+// Persistent kernel: one CTA per SM loops over output tiles (n fastest, so neighbouring CTAs share an A row
+// block in L2).  Two TMEM accumulator sets ([hi·hi | corrections], 2 x 256 columns) let the MMA issuer start the
+// next tile while the epilogue warps drain the previous one.
+//   warp 0      TMA producer (whole tile stream, 3-stage ring shared by all tiles)
+//   warp 1      TMEM allocation + single-thread MMA issue
+//   warps 2-5   epilogue (TMEM lane quarter = warp % 4)
+//   warps 6-9   RAW_A only: split the raw fp32 A tile into hi / lo in shared memory (in place + neighbouring slot,
+//               same swizzle), fence.proxy.async, then a 128-arrival `conv` mbarrier is the MMA issuer's go signal
 template <int EPI, bool RAW_A>
-__global__ void __launch_bounds__(TC_THREADS, 1)
+__global__ void __launch_bounds__(RAW_A ? TC_THREADS_RAW : TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constant__ CUtensorMap map_alo,
                const __grid_constant__ CUtensorMap map_bhi, const __grid_constant__ CUtensorMap map_blo,
                const TcParams p) {
   constexpr bool SYMMETRIC = (EPI == EPI_HIST || EPI == EPI_MINGT);
-  if (SYMMETRIC && blockIdx.x < blockIdx.y) return;  // mirrored tile counted with weight 2
 
   extern __shared__ unsigned char tc_smem_raw[];
   unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)tc_smem_raw + 1023) & ~(uintptr_t)1023);
-  uint64_t *full = reinterpret_cast<uint64_t *>(smem + TC_STAGES * TC_STAGE_BYTES);
+  float *stg_all = reinterpret_cast<float *>(smem + TC_STAGES * TC_STAGE_BYTES);
+  uint64_t *full = reinterpret_cast<uint64_t *>(smem + TC_STAGES * TC_STAGE_BYTES + TC_STG_BYTES);
   uint64_t *empty = full + TC_STAGES;
-  uint64_t *acc_ready = empty + TC_STAGES;
-  uint64_t *conv = acc_ready + 1;
-  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(conv + TC_STAGES);
+  uint64_t *conv = empty + TC_STAGES;
+  uint64_t *acc_full = conv + TC_STAGES;
+  uint64_t *acc_empty = acc_full + 2;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + 2);
   __shared__ unsigned int sh_hist[SYMMETRIC ? GHIST_BINS : 1];
   __shared__ double red[4];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const int64_t m0 = (int64_t)blockIdx.y * TC_BM, n0 = (int64_t)blockIdx.x * TC_BN;
-  int64_t k_begin = 0, k_end = p.k;
-  if (EPI == EPI_SPLITK) {
-    k_begin = (int64_t)blockIdx.z * p.k_per_split;
-    k_end = min(p.k, k_begin + p.k_per_split);
-  }
-  const int nkb = (int)((k_end - k_begin + TC_BK - 1) / TC_BK);  // >= 1 by construction of the grid
-  // hi·hi chunk boundaries (in k-blocks): chunk c covers [c*per, (c+1)*per)
-  const int per = (nkb + TC_KCHUNKS - 1) / TC_KCHUNKS;
+  const int64_t tiles_n = ceil_div<int64_t>(p.n, TC_BN), tiles_m = ceil_div<int64_t>(p.m, TC_BM);
+  const int64_t tiles_mn = tiles_m * tiles_n;
+  const int64_t n_tiles = tiles_mn * p.splits;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < TC_STAGES; ++s) {
@@ -198,7 +217,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constan
       tc::mbar_init(&empty[s], 1);
       tc::mbar_init(&conv[s], 128);
     }
-    tc::mbar_init(acc_ready, 1);
+    for (int a = 0; a < 2; ++a) {
+      tc::mbar_init(&acc_full[a], 1);
+      tc::mbar_init(&acc_empty[a], 4);
+    }
     tc::mbar_fence_init();
     tc::tma_prefetch_desc(&map_ahi);
     tc::tma_prefetch_desc(&map_alo);
@@ -206,75 +228,183 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constan
     tc::tma_prefetch_desc(&map_blo);
   }
   if (SYMMETRIC)
-    for (int i = threadIdx.x; i < GHIST_BINS; i += TC_THREADS) sh_hist[i] = 0u;
+    for (int i = threadIdx.x; i < GHIST_BINS; i += blockDim.x) sh_hist[i] = 0u;
   if (warp == 1) tc::tmem_alloc(tmem_slot, 512);
   tc::tc_fence_before();
   __syncthreads();
   tc::tc_fence_after();
   const uint32_t tmem = *tmem_slot;
 
+  // every role walks the same tile sequence; `it` counts k-blocks, `tl` processed tiles of this CTA
+  auto tile_coords = [&](int64_t tile, int64_t &z, int64_t &mb, int64_t &nb, int &nkb, int64_t &k_begin) -> bool {
+    z = tile / tiles_mn;
+    const int64_t r = tile - z * tiles_mn;
+    mb = r / tiles_n;
+    nb = r - mb * tiles_n;
+    if (SYMMETRIC && nb < mb) return false;  // mirrored tile counted with weight 2
+    k_begin = 0;
+    int64_t k_end = p.k;
+    if (EPI == EPI_SPLITK) {
+      k_begin = z * p.k_per_split;
+      k_end = min(p.k, k_begin + p.k_per_split);
+    }
+    nkb = (int)((k_end - k_begin + TC_BK - 1) / TC_BK);  // >= 1 by construction of the split
+    return true;
+  };
+
   if (warp == 0) {
     // ===== TMA producer =====
     if (lane == 0) {
-      for (int kb = 0; kb < nkb; ++kb) {
-        const int s = kb % TC_STAGES;
-        const uint32_t ph = (uint32_t)(kb / TC_STAGES) & 1u;
-        tc::mbar_wait(&empty[s], ph ^ 1u);  // first lap passes immediately
-        unsigned char *st = smem + s * TC_STAGE_BYTES;
-        tc::mbar_expect_tx(&full[s], RAW_A ? 3 * TC_TILE_BYTES : TC_STAGE_BYTES);
-        const int32_t kc = (int32_t)(k_begin + (int64_t)kb * TC_BK);
-        if (RAW_A) {
-          if (kc < p.k_a2)
-            tc::tma_load_2d(st + 0 * TC_TILE_BYTES, &map_ahi, &full[s], kc, (int32_t)m0);
-          else
-            tc::tma_load_2d(st + 0 * TC_TILE_BYTES, &map_alo, &full[s], kc - (int32_t)p.k_a2, (int32_t)m0);
-        } else {
-          tc::tma_load_2d(st + 0 * TC_TILE_BYTES, &map_ahi, &full[s], kc, (int32_t)m0);
-          tc::tma_load_2d(st + 1 * TC_TILE_BYTES, &map_alo, &full[s], kc, (int32_t)m0);
+      uint32_t it = 0;
+      for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        int64_t z, mb, nb, k_begin;
+        int nkb;
+        if (!tile_coords(tile, z, mb, nb, nkb, k_begin)) continue;
+        const int32_t m0 = (int32_t)(mb * TC_BM), n0 = (int32_t)(nb * TC_BN);
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int s = it % TC_STAGES;
+          const uint32_t ph = (it / TC_STAGES) & 1u;
+          tc::mbar_wait(&empty[s], ph ^ 1u);  // first lap passes immediately
+          unsigned char *st = smem + s * TC_STAGE_BYTES;
+          tc::mbar_expect_tx(&full[s], RAW_A ? 3 * TC_TILE_BYTES : TC_STAGE_BYTES);
+          const int32_t kc = (int32_t)(k_begin + (int64_t)kb * TC_BK);
+          if (RAW_A) {
+            if (kc < p.k_a2)
+              tc::tma_load_2d(st + 0 * TC_TILE_BYTES, &map_ahi, &full[s], kc, m0);
+            else
+              tc::tma_load_2d(st + 0 * TC_TILE_BYTES, &map_alo, &full[s], kc - (int32_t)p.k_a2, m0);
+          } else {
+            tc::tma_load_2d(st + 0 * TC_TILE_BYTES, &map_ahi, &full[s], kc, m0);
+            tc::tma_load_2d(st + 1 * TC_TILE_BYTES, &map_alo, &full[s], kc, m0);
+          }
+          tc::tma_load_2d(st + 2 * TC_TILE_BYTES, &map_bhi, &full[s], kc, n0);
+          tc::tma_load_2d(st + 3 * TC_TILE_BYTES, &map_blo, &full[s], kc, n0);
         }
-        tc::tma_load_2d(st + 2 * TC_TILE_BYTES, &map_bhi, &full[s], kc, (int32_t)n0);
-        tc::tma_load_2d(st + 3 * TC_TILE_BYTES, &map_blo, &full[s], kc, (int32_t)n0);
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
     if (lane == 0) {
       constexpr uint32_t idesc = tc::idesc_tf32(TC_BM, TC_BN);
-      const uint32_t acc_corr = tmem + TC_KCHUNKS * TC_BN;  // columns [384, 512)
-      for (int kb = 0; kb < nkb; ++kb) {
-        const int s = kb % TC_STAGES;
-        const uint32_t ph = (uint32_t)(kb / TC_STAGES) & 1u;
-        tc::mbar_wait(RAW_A ? &conv[s] : &full[s], ph);
+      uint32_t it = 0, tl = 0;
+      for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        int64_t z, mb, nb, k_begin;
+        int nkb;
+        if (!tile_coords(tile, z, mb, nb, nkb, k_begin)) continue;
+        const uint32_t a = tl & 1u, aph = (tl >> 1) & 1u;
+        tc::mbar_wait(&acc_empty[a], aph ^ 1u);  // the epilogue has drained this set (first use passes)
         tc::tc_fence_after();
-        unsigned char *st = smem + s * TC_STAGE_BYTES;
-        const uint64_t d_ahi = tc::smem_desc_k_sw128(st + 0 * TC_TILE_BYTES);
-        const uint64_t d_alo = tc::smem_desc_k_sw128(st + 1 * TC_TILE_BYTES);
-        const uint64_t d_bhi = tc::smem_desc_k_sw128(st + 2 * TC_TILE_BYTES);
-        const uint64_t d_blo = tc::smem_desc_k_sw128(st + 3 * TC_TILE_BYTES);
-        const int chunk = kb / per;
-        const uint32_t acc_main = tmem + (uint32_t)chunk * TC_BN;
-        const bool first_of_chunk = (kb % per) == 0;
+        const uint32_t acc_main = tmem + a * (2 * TC_BN), acc_corr = acc_main + TC_BN;
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int s = it % TC_STAGES;
+          const uint32_t ph = (it / TC_STAGES) & 1u;
+          tc::mbar_wait(RAW_A ? &conv[s] : &full[s], ph);
+          tc::tc_fence_after();
+          unsigned char *st = smem + s * TC_STAGE_BYTES;
+          const uint64_t d_ahi = tc::smem_desc_k_sw128(st + 0 * TC_TILE_BYTES);
+          const uint64_t d_alo = tc::smem_desc_k_sw128(st + 1 * TC_TILE_BYTES);
+          const uint64_t d_bhi = tc::smem_desc_k_sw128(st + 2 * TC_TILE_BYTES);
+          const uint64_t d_blo = tc::smem_desc_k_sw128(st + 3 * TC_TILE_BYTES);
 #pragma unroll
-        for (int k = 0; k < TC_BK / 8; ++k) {
-          const uint32_t off = (uint32_t)k * 32u;  // 8 TF32 = 32 bytes inside the swizzled 128-byte row
-          tc::mma_tf32(acc_main, tc::smem_desc_advance(d_ahi, off), tc::smem_desc_advance(d_bhi, off), idesc,
-                       (first_of_chunk && k == 0) ? 0u : 1u);
-          tc::mma_tf32(acc_corr, tc::smem_desc_advance(d_ahi, off), tc::smem_desc_advance(d_blo, off), idesc,
-                       (kb == 0 && k == 0) ? 0u : 1u);
-          tc::mma_tf32(acc_corr, tc::smem_desc_advance(d_alo, off), tc::smem_desc_advance(d_bhi, off), idesc, 1u);
+          for (int k = 0; k < TC_BK / 8; ++k) {
+            const uint32_t off = (uint32_t)k * 32u;  // 8 TF32 = 32 bytes inside the swizzled 128-byte row
+            const uint32_t acc = (kb == 0 && k == 0) ? 0u : 1u;
+            tc::mma_tf32(acc_main, tc::smem_desc_advance(d_ahi, off), tc::smem_desc_advance(d_bhi, off), idesc, acc);
+            tc::mma_tf32(acc_corr, tc::smem_desc_advance(d_ahi, off), tc::smem_desc_advance(d_blo, off), idesc, acc);
+            tc::mma_tf32(acc_corr, tc::smem_desc_advance(d_alo, off), tc::smem_desc_advance(d_bhi, off), idesc, 1u);
+          }
+          tc::mma_commit(&empty[s]);  // frees the stage once these MMAs have read it
         }
-        tc::mma_commit(&empty[s]);  // frees the stage once these MMAs have read it
+        tc::mma_commit(&acc_full[a]);
+        ++tl;
       }
-      tc::mma_commit(acc_ready);
     }
-  } else {
+  } else if (warp < 6) {
     // ===== epilogue (warps 2..5; TMEM lane quarter = warp % 4) =====
     const int q = warp & 3;
-    if (RAW_A) {
-      const int t = threadIdx.x - 64;  // 0..127
-      for (int kb = 0; kb < nkb; ++kb) {
-        const int s = kb % TC_STAGES;
-        const uint32_t ph = (uint32_t)(kb / TC_STAGES) & 1u;
+    float *stg = stg_all + (warp - 2) * (32 * TC_STG_LD);
+    uint32_t tl = 0;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      int64_t z, mb, nb, k_begin;
+      int nkb;
+      if (!tile_coords(tile, z, mb, nb, nkb, k_begin)) continue;
+      const uint32_t a = tl & 1u, aph = (tl >> 1) & 1u;
+      tc::mbar_wait(&acc_full[a], aph);
+      tc::tc_fence_after();
+      const int64_t m0 = mb * TC_BM, n0 = nb * TC_BN;
+      const int64_t m_row = m0 + q * 32 + lane;  // the row this thread owns in the TMEM layout
+      const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16) + a * (2 * TC_BN);
+      double lsum = 0.0;
+      unsigned int best = 0xffffffffu;
+      const unsigned int wgt = (SYMMETRIC && nb != mb) ? 2u : 1u;
+#pragma unroll 1
+      for (int c0 = 0; c0 < TC_BN; c0 += 32) {
+        float v[32], t[32];
+        tc::tmem_ld_32x32(lane_base + (uint32_t)(TC_BN + c0), v);  // corrections first (smallest)
+        tc::tmem_ld_32x32(lane_base + (uint32_t)c0, t);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[j] += t[j];
+        if (c0 + 32 >= TC_BN) {  // last TMEM read of this set: hand it back to the MMA issuer
+          tc::tc_fence_before();
+          __syncwarp();
+          if (lane == 0) tc::mbar_arrive(&acc_empty[a]);
+        }
+        if (n0 + c0 >= p.n) continue;
+        if (EPI == EPI_HIST) {
+          if (m_row < p.m) {
+            const unsigned int prefix = p.g.sel->prefix, mask = p.g.sel->mask;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              if (n0 + c0 + j < p.n) {
+                const unsigned int key = f32_key(v[j]);
+                if ((key & mask) == prefix) atomicAdd(&sh_hist[(key >> p.g.shift) & p.g.bin_mask], wgt);
+              }
+            }
+          }
+        } else if (EPI == EPI_MINGT) {
+          if (m_row < p.m) {
+            const unsigned int base = p.g.sel->prefix;
+#pragma unroll
+            for (int j = 0; j < 32; ++j) {
+              if (n0 + c0 + j < p.n) {
+                const unsigned int key = f32_key(v[j]);
+                if (key > base) best = min(best, key);
+              }
+            }
+          }
+        } else {
+          __syncwarp();  // the previous block's staging reads are done
+#pragma unroll
+          for (int j = 0; j < 32; ++j) stg[lane * TC_STG_LD + j] = v[j];
+          __syncwarp();
+          tc_epilogue_block<EPI>(p, z, m0 + q * 32, n0 + c0, stg, lane, lsum);
+        }
+      }
+      if (EPI == EPI_GSS) {
+        lsum = warp_sum(lsum);
+        named_bar_sync(1, 128);  // the previous tile's partial has been consumed
+        if (lane == 0) red[q] = lsum;
+        named_bar_sync(1, 128);
+        if (warp == 2 && lane == 0) p.g.loss_partials[mb * tiles_n + nb] = (red[0] + red[1]) + (red[2] + red[3]);
+      }
+      if (EPI == EPI_MINGT) {
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
+        if (lane == 0 && best != 0xffffffffu) atomicMin(&p.g.sel_out->min_gt, best);
+      }
+      ++tl;
+    }
+  } else if (RAW_A) {
+    // ===== converter warps (6..9): raw fp32 A tile -> hi (in place) + lo (neighbouring slot) =====
+    const int t = threadIdx.x - 192;  // 0..127
+    uint32_t it = 0;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      int64_t z, mb, nb, k_begin;
+      int nkb;
+      if (!tile_coords(tile, z, mb, nb, nkb, k_begin)) continue;
+      for (int kb = 0; kb < nkb; ++kb, ++it) {
+        const int s = it % TC_STAGES;
+        const uint32_t ph = (it / TC_STAGES) & 1u;
         tc::mbar_wait(&full[s], ph);
         float4 *hi4 = reinterpret_cast<float4 *>(smem + s * TC_STAGE_BYTES);
         float4 *lo4 = reinterpret_cast<float4 *>(smem + s * TC_STAGE_BYTES + TC_TILE_BYTES);
@@ -293,33 +423,6 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constan
         tc::mbar_arrive(&conv[s]);
       }
     }
-    tc::mbar_wait(acc_ready, 0u);
-    tc::tc_fence_after();
-    const int64_t m = m0 + q * 32 + lane;
-    const int nchunks = (nkb + per - 1) / per;  // hi·hi accumulators actually written
-    double lsum = 0.0;
-    unsigned int best = 0xffffffffu;
-#pragma unroll 1
-    for (int c0 = 0; c0 < TC_BN; c0 += 32) {
-      const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16);
-      float v[32], t[32];
-      tc::tmem_ld_32x32(lane_base + (uint32_t)(TC_KCHUNKS * TC_BN + c0), v);  // corrections first (smallest)
-      for (int c = nchunks - 1; c >= 0; --c) {
-        tc::tmem_ld_32x32(lane_base + (uint32_t)(c * TC_BN + c0), t);
-#pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] += t[j];
-      }
-      if (m < p.m && n0 + c0 < p.n) tc_epilogue_row<EPI>(p, m, n0 + c0, v, lsum, sh_hist, best);
-    }
-    if (EPI == EPI_GSS) {
-      lsum = warp_sum(lsum);
-      if (lane == 0) red[q] = lsum;
-    }
-    if (EPI == EPI_MINGT) {
-#pragma unroll
-      for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
-      if (lane == 0 && best != 0xffffffffu) atomicMin(&p.g.sel_out->min_gt, best);
-    }
   }
 
   tc::tc_fence_before();
@@ -328,13 +431,10 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constan
     tc::tc_fence_after();
     tc::tmem_dealloc(tmem, 512);
   }
-  if (EPI == EPI_GSS && threadIdx.x == 0)
-    p.g.loss_partials[(int64_t)blockIdx.y * gridDim.x + blockIdx.x] = (red[0] + red[1]) + (red[2] + red[3]);
   if (EPI == EPI_HIST) {
-    const unsigned long long w = (blockIdx.x == blockIdx.y) ? 1ull : 2ull;
-    for (int i = threadIdx.x; i < GHIST_BINS; i += TC_THREADS) {
+    for (int i = threadIdx.x; i < GHIST_BINS; i += blockDim.x) {
       const unsigned int c = sh_hist[i];
-      if (c) atomicAdd(p.g.hist + i, w * c);
+      if (c) atomicAdd(p.g.hist + i, (unsigned long long)c);
     }
   }
 }
@@ -405,15 +505,17 @@ static int launch_gemm_tc(const float *ahi, const float *alo, const float *bhi, 
   if ((rc = make_operand_map(&mb, bhi, n, k, ldb))) return rc;
   if ((rc = make_operand_map(&mbl, blo, n, k, ldb))) return rc;
   TcParams p{};
-  p.m = m; p.n = n; p.k = k; p.k_per_split = k_per_split; p.k_a2 = RAW_A ? k_a2 : k; p.g = g;
+  p.m = m; p.n = n; p.k = k; p.k_per_split = k_per_split; p.splits = splits > 0 ? splits : 1;
+  p.k_a2 = RAW_A ? k_a2 : k; p.g = g;
   static bool attr_set = false;  // per template instance
   if (!attr_set) {
     GDR_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<EPI, RAW_A>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   TC_SMEM_BYTES));
     attr_set = true;
   }
-  dim3 grid((unsigned)ceil_div<int64_t>(n, TC_BN), (unsigned)ceil_div<int64_t>(m, TC_BM), (unsigned)splits);
-  gemm_tc_kernel<EPI, RAW_A><<<grid, TC_THREADS, TC_SMEM_BYTES, st>>>(ma, ml, mb, mbl, p);
+  const int64_t tiles = ceil_div<int64_t>(n, TC_BN) * ceil_div<int64_t>(m, TC_BM) * p.splits;
+  const unsigned grid = (unsigned)std::min<int64_t>(tiles, kNumSMs);  // persistent: one CTA per SM walks the tiles
+  gemm_tc_kernel<EPI, RAW_A><<<grid, RAW_A ? TC_THREADS_RAW : TC_THREADS, TC_SMEM_BYTES, st>>>(ma, ml, mb, mbl, p);
   GDR_LAUNCHED();
   return GDR_OK;
 }
