@@ -4,25 +4,18 @@
 //
 // Why not plain TF32: the reference runs these contractions in fp32 (torch.mm / nn.Linear / np.dot,
 // modules/model.py:163-173, 218-221) and parity is 1e-5 relative.  Each operand is therefore split as
-// x = hi + lo with hi = rn_tf32(x), lo = rn_tf32(x - hi) (split_tf32_kernel, exact residual), and the
-// product is evaluated as  hi·hi  +  (hi·lo + lo·hi)  — three TF32 MMAs per K step ("3xTF32").  The
-// dropped lo·lo term and the rounding of lo are both <= 2^-22 relative per term.  The small correction
-// products accumulate in their OWN TMEM accumulator (their rounding errors are 2^-11 smaller) and are
-// added to the hi·hi accumulator in round-to-nearest fp32 in the epilogue.
+// x = hi + lo with hi = rn_tf32(x), lo = rn_tf32(x - hi) (exact residual), and the product is evaluated as
+// hi·hi  +  (hi·lo + lo·hi)  — "3xTF32".  The dropped lo·lo term and the rounding of lo are both <= 2^-22
+// relative per term.  The small correction products accumulate in their OWN TMEM accumulator and are added to
+// the hi·hi accumulator in round-to-nearest fp32 in the epilogue.
 //
-// Structure: persistent kernel, one CTA per SM walking 128 x 128 output tiles; see gemm_tc_kernel below.
-//   warp 0    TMA producer: four tiles per stage (A_hi, A_lo, B_hi, B_lo; 128 rows x 32 fp32 = 128-byte rows,
-//             SWIZZLE_128B) into a 3-stage ring, completion on `full` mbarriers
-//   warp 1    allocates 512 TMEM columns = two accumulator sets [hi·hi | corrections]; one elected lane issues
-//             tcgen05.mma (kind::tf32, M=128, N=128, K=8) 12 times per stage, releases the stage with
-//             tcgen05.commit -> `empty`, and the tile with tcgen05.commit -> `acc_full`
-//   warps 2-5 epilogue: tcgen05.ld (32 lanes x 32 columns), sum of the two accumulators, transposition through
-//             shared memory, fused epilogue (bias / ELU / residual, GSS loss + dG, split-K partials, radix
-//             histogram) with coalesced stores; overlaps the next tile's main loop (`acc_empty`)
-//   warps 6-9 (RAW_A) split the raw fp32 A tile into hi / lo in shared memory
-// Measured (tests/test_gpu_tc.py): one hi·hi accumulator per tile keeps the error at 4-6e-7 of sum|a||b|, the level
-// of torch-CPU / cuBLAS fp32 (2-5e-7); round 1 cut the chain into three accumulators (1.4-3.1e-7) but that used all
-// 512 TMEM columns for one tile and left the epilogue un-overlapped.
+// Structure: persistent warp-specialised kernel, one CTA per SM walking 128 x 128 output tiles (gemm_tc_kernel):
+// TMA producer warp, single-thread MMA issuer, eight epilogue warps, and — when A arrives as plain fp32 (RAW_A) —
+// four converter warps that split A on the fly and feed it to the MMAs through TENSOR MEMORY, so that the only
+// shared-memory MMA operand is B.  Measured at the MSI layer shape 29,959 x 256 x 512 (profiles/tc_pipeline_trace.py,
+// CTA-0 clock stamps): 888 clk per k-block in the main loop (12 x 64 = 768 is the tensor-pipe floor), 68.6 us for
+// the layer forward with the weight split, 105.5 us before the A-in-TMEM / 8-warp epilogue change.
+// Accuracy (tests/test_gpu_tc.py): max error 3-8e-7 of sum|a||b| (torch-CPU fp32: 2-5e-7).
 #include <algorithm>
 
 #include "gemm_tc.cuh"
@@ -30,12 +23,17 @@
 
 namespace gdr {
 
-constexpr int TC_BM = 128, TC_BN = 128, TC_BK = 32, TC_STAGES = 3;
-constexpr int TC_THREADS = 192, TC_THREADS_RAW = 320;         // + 4 converter warps when A is split in the kernel
+constexpr int TC_BM = 128, TC_BN = 128, TC_BK = 32;
+constexpr int TC_STAGES = 3, TC_STAGES_RAW = 4;               // pre-split: 4 tiles per stage; RAW_A: 3 tiles per stage
+constexpr int TC_EPI_WARPS = 8;                               // two per TMEM lane quarter: 64 columns each
+constexpr int TC_THREADS = 64 + 32 * TC_EPI_WARPS;            // producer, MMA issuer, epilogue warps
+constexpr int TC_THREADS_RAW = TC_THREADS + 128;              // + 4 converter warps when A is split in the kernel
 constexpr int TC_TILE_BYTES = TC_BM * TC_BK * 4;              // 16 KB per operand tile
-constexpr int TC_STAGE_BYTES = 4 * TC_TILE_BYTES;             // A_hi, A_lo, B_hi, B_lo
-constexpr int TC_STG_BYTES = 4 * 32 * 33 * 4;                 // per-warp 32 x 33 transposition buffers of the epilogue
-constexpr int TC_SMEM_BYTES = TC_STAGES * TC_STAGE_BYTES + TC_STG_BYTES + 1024 /*alignment slack*/ + 256 /*barriers*/;
+constexpr int TC_RING_BYTES = TC_STAGES * 4 * TC_TILE_BYTES;   // = TC_STAGES_RAW * 3 * TC_TILE_BYTES = 192 KB
+constexpr int TC_STG_BYTES = TC_EPI_WARPS * 32 * 32 * 4;      // per-warp 32 x 32 transposition buffers of the epilogue
+constexpr int tc_smem_bytes(bool staging) {
+  return TC_RING_BYTES + (staging ? TC_STG_BYTES : 0) + 1024 /*alignment slack*/ + 512 /*barriers*/;
+}
 
 struct TcParams {
   int64_t m, n, k;         // k = full reduction length (all of it unless split-K)
@@ -43,7 +41,14 @@ struct TcParams {
   int64_t splits;          // EPI_SPLITK: number of K ranges (tiles = tiles_m * tiles_n * splits); otherwise 1
   int64_t k_a2;            // RAW_A: columns [k_a2, k) of A come from the second raw source (k_a2 % TC_BK == 0)
   GemmParams g;            // epilogue operands, same meaning as in gemm_simt.cuh (a/b/lda/ldb unused)
+  long long *trace;        // diagnostic: CTA 0 records clock64() at the pipeline hand-offs (gdr_debug_tc_trace)
 };
+
+// trace[role][index < 128][event < 4]; roles: 0 TMA producer, 1 MMA issuer, 2 converter (warp 6), 3 epilogue (warp 2)
+__device__ __forceinline__ void tc_trace(const TcParams &p, int role, uint32_t idx, int ev) {
+  if (p.trace != nullptr && blockIdx.x == 0 && idx < 128u) p.trace[(role * 128 + (int)idx) * 4 + ev] = clock64();
+}
+static long long *g_tc_trace = nullptr;
 
 // ---- operand split ---------------------------------------------------------------------------------
 __device__ __forceinline__ float rn_tf32(float x) {
@@ -98,79 +103,84 @@ split_tf32_transpose_kernel(const float *__restrict__ s, int64_t ld, int64_t row
 
 // ---- fused epilogues ---------------------------------------------------------------------------------------
 // After the TMEM read a thread owns 32 consecutive columns of ONE output row; stores in that layout would touch
-// 32 different rows per instruction.  Each epilogue warp therefore transposes its 32x32 block through a padded
+// 32 different rows per instruction.  Each epilogue warp therefore transposes its 32x32 block through a
 // shared-memory buffer and works on it as 8 steps of 4 rows x 32 columns: lane l owns columns 4*(l%8)..+3 of
-// row 4*i + l/8, so every global load / store of the warp covers 4 row segments of 128 contiguous bytes, and the
-// loads of all 8 steps (residual, addend, bias) are issued before any of them is consumed.
-constexpr int TC_STG_LD = 33;  // padded row length of the staging buffer (bank-conflict free both ways)
+// row 4*i + l/8, so every global load / store of the warp covers 4 row segments of 128 contiguous bytes; the
+// addend loads (residual, e1/e2) of 4 steps are issued together before any of them is consumed.
+// The staging buffer is 32 rows x 8 chunks of 16 bytes, chunk c of row r stored at position c ^ (r % 8): the
+// row-per-thread writes and the 4-rows-per-instruction reads are both conflict-free 128-bit accesses.
+__device__ __forceinline__ uint32_t tc_stg_off(int row, int chunk) { return (uint32_t)(row * 8 + (chunk ^ (row & 7))) << 4; }
 
 template <int EPI>
 __device__ __forceinline__ void tc_epilogue_block(const TcParams &p, int64_t z, int64_t m_base, int64_t n_base,
-                                                  const float *__restrict__ stg, int lane, double &lsum) {
+                                                  uint32_t stg, int lane, double &lsum) {
   const GemmParams &g = p.g;
   const int rq = lane >> 3, cq = (lane & 7) * 4;
   const int64_t nn = n_base + cq;
   const int64_t n_lim = (EPI == EPI_GSS) ? g.ldc : p.n;  // every other caller has n % 4 == 0
   if (nn >= n_lim) return;
-  float4 add1[8], add2[8];
   float4 bias = make_float4(0.f, 0.f, 0.f, 0.f);
   if (EPI == EPI_LAYER) {
     const float4 b1 = ldg_f4(g.bias1 + nn), b2 = ldg_f4(g.bias2 + nn);
     bias = make_float4(b1.x + b2.x, b1.y + b2.y, b1.z + b2.z, b1.w + b2.w);
   }
   const bool has_add = (EPI == EPI_STORE && g.e1 != nullptr) || (EPI == EPI_LAYER && g.residual != nullptr);
-  if (has_add) {
 #pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const int64_t m = m_base + i * 4 + rq;
-      if (m < p.m) {
-        if (EPI == EPI_STORE) {
-          add1[i] = ldg_f4(g.e1 + m * g.ldc + nn);
-          add2[i] = ldg_f4(g.e2 + m * g.ldc + nn);
-        } else {
-          add1[i] = ldg_f4(g.residual + m * g.ldc + nn);
+  for (int h = 0; h < 2; ++h) {  // two batches of 4 steps: the addend loads of a batch are in flight together
+    float4 add1[4], add2[4];
+    if (has_add) {
+#pragma unroll
+      for (int i = 0; i < 4; ++i) {
+        const int64_t m = m_base + (h * 4 + i) * 4 + rq;
+        if (m < p.m) {
+          if (EPI == EPI_STORE) {
+            add1[i] = ldg_f4(g.e1 + m * g.ldc + nn);
+            add2[i] = ldg_f4(g.e2 + m * g.ldc + nn);
+          } else {
+            add1[i] = ldg_f4(g.residual + m * g.ldc + nn);
+          }
         }
       }
     }
-  }
 #pragma unroll
-  for (int i = 0; i < 8; ++i) {
-    const int r = i * 4 + rq;
-    const int64_t m = m_base + r;
-    if (m >= p.m) continue;
-    const float *sp = stg + r * TC_STG_LD + cq;
-    float a0 = sp[0], a1 = sp[1], a2 = sp[2], a3 = sp[3];
-    if (EPI == EPI_GSS) {
-      float v[4] = {a0, a1, a2, a3};
+    for (int i = 0; i < 4; ++i) {
+      const int r = (h * 4 + i) * 4 + rq;
+      const int64_t m = m_base + r;
+      if (m >= p.m) continue;
+      const float4 sv = tc::lds_f4(stg + tc_stg_off(r, lane & 7));
+      float a0 = sv.x, a1 = sv.y, a2 = sv.z, a3 = sv.w;
+      if (EPI == EPI_GSS) {
+        float v[4] = {a0, a1, a2, a3};
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        float w = 0.f;
-        if (nn + j < p.n) {
-          const float gv = v[j];
-          const float rr = fmaxf(gv, 0.f) - g.beta;
-          lsum += (double)(-0.5f * g.alpha * rr * rr);
-          w = gv > 0.f ? -g.alpha * rr * g.wscale : 0.f;
+        for (int j = 0; j < 4; ++j) {
+          float w = 0.f;
+          if (nn + j < p.n) {
+            const float gv = v[j];
+            const float rr = fmaxf(gv, 0.f) - g.beta;
+            lsum += (double)(-0.5f * g.alpha * rr * rr);
+            w = gv > 0.f ? -g.alpha * rr * g.wscale : 0.f;
+          }
+          v[j] = w;
         }
-        v[j] = w;
+        a0 = v[0]; a1 = v[1]; a2 = v[2]; a3 = v[3];
       }
-      a0 = v[0]; a1 = v[1]; a2 = v[2]; a3 = v[3];
-    }
-    if (EPI == EPI_STORE && has_add) {
-      a0 = fmaf(add1[i].x, add2[i].x, a0); a1 = fmaf(add1[i].y, add2[i].y, a1);
-      a2 = fmaf(add1[i].z, add2[i].z, a2); a3 = fmaf(add1[i].w, add2[i].w, a3);
-    }
-    if (EPI == EPI_LAYER) {
-      a0 += bias.x; a1 += bias.y; a2 += bias.z; a3 += bias.w;
-    }
-    float *crow = g.c + (EPI == EPI_SPLITK ? (z * p.m + m) : m) * g.ldc + nn;
-    *reinterpret_cast<float4 *>(crow) = make_float4(a0, a1, a2, a3);
-    if (EPI == EPI_LAYER) {
-      float y0 = elu1(a0), y1 = elu1(a1), y2 = elu1(a2), y3 = elu1(a3);
-      if (has_add) {
-        y0 = fmaf(g.decay, y0, add1[i].x); y1 = fmaf(g.decay, y1, add1[i].y);
-        y2 = fmaf(g.decay, y2, add1[i].z); y3 = fmaf(g.decay, y3, add1[i].w);
+      if (EPI == EPI_STORE && has_add) {
+        a0 = fmaf(add1[i].x, add2[i].x, a0); a1 = fmaf(add1[i].y, add2[i].y, a1);
+        a2 = fmaf(add1[i].z, add2[i].z, a2); a3 = fmaf(add1[i].w, add2[i].w, a3);
       }
-      *reinterpret_cast<float4 *>(g.xnext + m * g.ldc + nn) = make_float4(y0, y1, y2, y3);
+      if (EPI == EPI_LAYER) {
+        a0 += bias.x; a1 += bias.y; a2 += bias.z; a3 += bias.w;
+      }
+      float *crow = g.c + (EPI == EPI_SPLITK ? (z * p.m + m) : m) * g.ldc + nn;
+      *reinterpret_cast<float4 *>(crow) = make_float4(a0, a1, a2, a3);
+      if (EPI == EPI_LAYER) {
+        float y0 = elu1(a0), y1 = elu1(a1), y2 = elu1(a2), y3 = elu1(a3);
+        if (has_add) {
+          y0 = fmaf(g.decay, y0, add1[i].x); y1 = fmaf(g.decay, y1, add1[i].y);
+          y2 = fmaf(g.decay, y2, add1[i].z); y3 = fmaf(g.decay, y3, add1[i].w);
+        }
+        *reinterpret_cast<float4 *>(g.xnext + m * g.ldc + nn) = make_float4(y0, y1, y2, y3);
+      }
     }
   }
 }
@@ -180,31 +190,52 @@ __device__ __forceinline__ void named_bar_sync(int id, int threads) {
 }
 
 // Persistent kernel: one CTA per SM loops over output tiles (n fastest, so neighbouring CTAs share an A row
-// block in L2).  Two TMEM accumulator sets ([hi·hi | corrections], 2 x 256 columns) let the MMA issuer start the
-// next tile while the epilogue warps drain the previous one.
-//   warp 0      TMA producer (whole tile stream, 3-stage ring shared by all tiles)
-//   warp 1      TMEM allocation + single-thread MMA issue
-//   warps 2-5   epilogue (TMEM lane quarter = warp % 4)
-//   warps 6-9   RAW_A only: split the raw fp32 A tile into hi / lo in shared memory (in place + neighbouring slot,
-//               same swizzle), fence.proxy.async, then a 128-arrival `conv` mbarrier is the MMA issuer's go signal
+// block in L2).
+//   warp 0        TMA producer (whole tile stream, one ring shared by all tiles)
+//   warp 1        TMEM allocation + single-thread MMA issue
+//   warps 2-9     epilogue: two warps per TMEM lane quarter, 64 accumulator columns each.  A warp first DRAINS its
+//                 columns (main + corrections, summed in fp32 RN) into registers and hands the accumulator back
+//                 (`acc_empty`), then does the global-memory part of the epilogue from registers while the MMA
+//                 issuer is already inside the next tile.
+//   warps 10-13   RAW_A only: operand A never becomes a shared-memory MMA operand.  TMA lands the raw fp32 tile
+//                 (128 rows x 32 columns, SWIZZLE_128B); each converter thread owns one row: 8 conflict-free
+//                 LDS.128, hi = rn_tf32(x), lo = rn_tf32(x - hi), tcgen05.st into a 4-deep TMEM ring (64 columns
+//                 per stage: hi | lo), and the MMAs read A from tensor memory (tcgen05.mma [d], [a], b-desc).
+// Shared-memory traffic per k-block: pre-split form 64 KB TMA + 96 KB operand reads; RAW_A form 48 KB TMA + 16 KB
+// converter reads + 48 KB B reads — the SS form of kind::tf32 at M = N = 128 needs the full 128 B/clk for its
+// operand reads alone.
+// TMEM columns:  pre-split  [set0 main | set0 corr | set1 main | set1 corr]      (2 accumulator sets)
+//                RAW_A      [main | corr | A ring: 4 x (hi 32 | lo 32)]          (1 set; the drain into registers
+//                           costs the MMA pipe ~1k of the ~17k clocks of a K = 512 tile)
+// The hi·hi products and the corrections keep separate accumulators: the tensor core truncates when it adds into
+// the accumulator, so the error grows with the number of MMAs that hit the LARGE accumulator (measured: one shared
+// accumulator, 192 adds at K = 512, 2.1e-6 of sum|a||b|; separate, 64 adds, 8e-7).
 template <int EPI, bool RAW_A>
 __global__ void __launch_bounds__(RAW_A ? TC_THREADS_RAW : TC_THREADS, 1)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constant__ CUtensorMap map_alo,
                const __grid_constant__ CUtensorMap map_bhi, const __grid_constant__ CUtensorMap map_blo,
                const TcParams p) {
   constexpr bool SYMMETRIC = (EPI == EPI_HIST || EPI == EPI_MINGT);
+  constexpr int STAGES = RAW_A ? TC_STAGES_RAW : TC_STAGES;
+  constexpr int STAGE_BYTES = RAW_A ? 3 * TC_TILE_BYTES : 4 * TC_TILE_BYTES;  // RAW_A: A raw, B_hi, B_lo
+  constexpr uint32_t ACC_SETS = RAW_A ? 1 : 2;                                // [main | corr] pairs of 2 * TC_BN columns
+  constexpr uint32_t A_RING_COL = 2 * TC_BN;                                  // RAW_A: first column of the A ring
+  constexpr bool STAGING = !SYMMETRIC;                                        // histogram epilogues never store tiles
+  static_assert(STAGES * STAGE_BYTES == TC_RING_BYTES, "both forms use the same ring size");
 
   extern __shared__ unsigned char tc_smem_raw[];
-  unsigned char *smem = reinterpret_cast<unsigned char *>(((uintptr_t)tc_smem_raw + 1023) & ~(uintptr_t)1023);
-  float *stg_all = reinterpret_cast<float *>(smem + TC_STAGES * TC_STAGE_BYTES);
-  uint64_t *full = reinterpret_cast<uint64_t *>(smem + TC_STAGES * TC_STAGE_BYTES + TC_STG_BYTES);
-  uint64_t *empty = full + TC_STAGES;
-  uint64_t *conv = empty + TC_STAGES;
-  uint64_t *acc_full = conv + TC_STAGES;
+  unsigned char *smem = tc_smem_raw + ((1024u - (tc::smem_u32(tc_smem_raw) & 1023u)) & 1023u);
+  uint64_t *full = reinterpret_cast<uint64_t *>(smem + TC_RING_BYTES + (STAGING ? TC_STG_BYTES : 0));
+  uint64_t *empty = full + 4;    // B (and pre-split A) stage consumed by the MMAs
+  uint64_t *afull = empty + 4;   // RAW_A: raw A tile landed
+  uint64_t *aempty = afull + 4;  // RAW_A: raw A tile read by the converter warps
+  uint64_t *tfull = aempty + 4;  // RAW_A: hi/lo of the stage are in tensor memory
+  uint64_t *tempty = tfull + 4;  // RAW_A: the MMAs have read that TMEM stage
+  uint64_t *acc_full = tempty + 4;
   uint64_t *acc_empty = acc_full + 2;
   uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + 2);
   __shared__ unsigned int sh_hist[SYMMETRIC ? GHIST_BINS : 1];
-  __shared__ double red[4];
+  __shared__ double red[TC_EPI_WARPS];
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int64_t tiles_n = ceil_div<int64_t>(p.n, TC_BN), tiles_m = ceil_div<int64_t>(p.m, TC_BM);
@@ -212,14 +243,17 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constan
   const int64_t n_tiles = tiles_mn * p.splits;
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < TC_STAGES; ++s) {
+    for (int s = 0; s < 4; ++s) {
       tc::mbar_init(&full[s], 1);
       tc::mbar_init(&empty[s], 1);
-      tc::mbar_init(&conv[s], 128);
+      tc::mbar_init(&afull[s], 1);
+      tc::mbar_init(&aempty[s], 128);
+      tc::mbar_init(&tfull[s], 128);
+      tc::mbar_init(&tempty[s], 1);
     }
     for (int a = 0; a < 2; ++a) {
       tc::mbar_init(&acc_full[a], 1);
-      tc::mbar_init(&acc_empty[a], 4);
+      tc::mbar_init(&acc_empty[a], TC_EPI_WARPS);
     }
     tc::mbar_fence_init();
     tc::tma_prefetch_desc(&map_ahi);
@@ -262,101 +296,137 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constan
         if (!tile_coords(tile, z, mb, nb, nkb, k_begin)) continue;
         const int32_t m0 = (int32_t)(mb * TC_BM), n0 = (int32_t)(nb * TC_BN);
         for (int kb = 0; kb < nkb; ++kb, ++it) {
-          const int s = it % TC_STAGES;
-          const uint32_t ph = (it / TC_STAGES) & 1u;
-          tc::mbar_wait(&empty[s], ph ^ 1u);  // first lap passes immediately
-          unsigned char *st = smem + s * TC_STAGE_BYTES;
-          tc::mbar_expect_tx(&full[s], RAW_A ? 3 * TC_TILE_BYTES : TC_STAGE_BYTES);
+          const int s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1u;
+          unsigned char *st = smem + s * STAGE_BYTES;
           const int32_t kc = (int32_t)(k_begin + (int64_t)kb * TC_BK);
           if (RAW_A) {
+            tc::mbar_wait(&aempty[s], ph ^ 1u);  // first lap passes immediately
+            tc_trace(p, 0, it, 0);
+            tc::mbar_expect_tx(&afull[s], TC_TILE_BYTES);
             if (kc < p.k_a2)
-              tc::tma_load_2d(st + 0 * TC_TILE_BYTES, &map_ahi, &full[s], kc, m0);
+              tc::tma_load_2d(st, &map_ahi, &afull[s], kc, m0);
             else
-              tc::tma_load_2d(st + 0 * TC_TILE_BYTES, &map_alo, &full[s], kc - (int32_t)p.k_a2, m0);
+              tc::tma_load_2d(st, &map_alo, &afull[s], kc - (int32_t)p.k_a2, m0);
+            tc::mbar_wait(&empty[s], ph ^ 1u);
+            tc_trace(p, 0, it, 1);
+            tc::mbar_expect_tx(&full[s], 2 * TC_TILE_BYTES);
+            tc::tma_load_2d(st + 1 * TC_TILE_BYTES, &map_bhi, &full[s], kc, n0);
+            tc::tma_load_2d(st + 2 * TC_TILE_BYTES, &map_blo, &full[s], kc, n0);
+            tc_trace(p, 0, it, 2);
           } else {
+            tc::mbar_wait(&empty[s], ph ^ 1u);
+            tc::mbar_expect_tx(&full[s], 4 * TC_TILE_BYTES);
             tc::tma_load_2d(st + 0 * TC_TILE_BYTES, &map_ahi, &full[s], kc, m0);
             tc::tma_load_2d(st + 1 * TC_TILE_BYTES, &map_alo, &full[s], kc, m0);
+            tc::tma_load_2d(st + 2 * TC_TILE_BYTES, &map_bhi, &full[s], kc, n0);
+            tc::tma_load_2d(st + 3 * TC_TILE_BYTES, &map_blo, &full[s], kc, n0);
           }
-          tc::tma_load_2d(st + 2 * TC_TILE_BYTES, &map_bhi, &full[s], kc, n0);
-          tc::tma_load_2d(st + 3 * TC_TILE_BYTES, &map_blo, &full[s], kc, n0);
         }
       }
     }
   } else if (warp == 1) {
     // ===== MMA issuer =====
     if (lane == 0) {
-      constexpr uint32_t idesc = tc::idesc_tf32(TC_BM, TC_BN);
+      constexpr uint32_t idesc = tc::idesc_tf32(TC_BM, TC_BN), idesc2 = tc::idesc_tf32(TC_BM, 2 * TC_BN);
+      (void)idesc2;
       uint32_t it = 0, tl = 0;
       for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         int64_t z, mb, nb, k_begin;
         int nkb;
         if (!tile_coords(tile, z, mb, nb, nkb, k_begin)) continue;
-        const uint32_t a = tl & 1u, aph = (tl >> 1) & 1u;
+        const uint32_t a = tl % ACC_SETS, aph = (tl / ACC_SETS) & 1u;
         tc::mbar_wait(&acc_empty[a], aph ^ 1u);  // the epilogue has drained this set (first use passes)
         tc::tc_fence_after();
         const uint32_t acc_main = tmem + a * (2 * TC_BN), acc_corr = acc_main + TC_BN;
         for (int kb = 0; kb < nkb; ++kb, ++it) {
-          const int s = it % TC_STAGES;
-          const uint32_t ph = (it / TC_STAGES) & 1u;
-          tc::mbar_wait(RAW_A ? &conv[s] : &full[s], ph);
-          tc::tc_fence_after();
-          unsigned char *st = smem + s * TC_STAGE_BYTES;
-          const uint64_t d_ahi = tc::smem_desc_k_sw128(st + 0 * TC_TILE_BYTES);
-          const uint64_t d_alo = tc::smem_desc_k_sw128(st + 1 * TC_TILE_BYTES);
-          const uint64_t d_bhi = tc::smem_desc_k_sw128(st + 2 * TC_TILE_BYTES);
-          const uint64_t d_blo = tc::smem_desc_k_sw128(st + 3 * TC_TILE_BYTES);
+          const int s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1u;
+          unsigned char *st = smem + s * STAGE_BYTES;
+          if (RAW_A) {
+            tc::mbar_wait(&full[s], ph);
+            tc_trace(p, 1, it, 0);
+            tc::mbar_wait(&tfull[s], ph);
+            tc_trace(p, 1, it, 1);
+            tc::tc_fence_after();
+            const uint32_t t_hi = tmem + A_RING_COL + (uint32_t)s * 64u, t_lo = t_hi + 32u;
+            const uint64_t d_bhi = tc::smem_desc_k_sw128(st + 1 * TC_TILE_BYTES);  // B_lo follows at + 16 KB
 #pragma unroll
-          for (int k = 0; k < TC_BK / 8; ++k) {
-            const uint32_t off = (uint32_t)k * 32u;  // 8 TF32 = 32 bytes inside the swizzled 128-byte row
-            const uint32_t acc = (kb == 0 && k == 0) ? 0u : 1u;
-            tc::mma_tf32(acc_main, tc::smem_desc_advance(d_ahi, off), tc::smem_desc_advance(d_bhi, off), idesc, acc);
-            tc::mma_tf32(acc_corr, tc::smem_desc_advance(d_ahi, off), tc::smem_desc_advance(d_blo, off), idesc, acc);
-            tc::mma_tf32(acc_corr, tc::smem_desc_advance(d_alo, off), tc::smem_desc_advance(d_bhi, off), idesc, 1u);
+            for (int k = 0; k < TC_BK / 8; ++k) {
+              const uint32_t off = (uint32_t)k * 32u, col = (uint32_t)k * 8u;  // 8 TF32 = 32 bytes = 8 TMEM columns
+              const uint32_t acc = (kb == 0 && k == 0) ? 0u : 1u;
+              // B_hi and B_lo are adjacent 128-row tiles: one N = 256 MMA writes [hi·hi | hi·lo] into [main | corr]
+              tc::mma_tf32_ts(acc_main, t_hi + col, tc::smem_desc_advance(d_bhi, off), idesc2, acc);
+              tc::mma_tf32_ts(acc_corr, t_lo + col, tc::smem_desc_advance(d_bhi, off), idesc, 1u);
+            }
+            tc::mma_commit(&empty[s]);   // B stage free once these MMAs have read it
+            tc::mma_commit(&tempty[s]);  // and so is the TMEM stage of A
+            tc_trace(p, 1, it, 2);
+          } else {
+            tc::mbar_wait(&full[s], ph);
+            tc::tc_fence_after();
+            const uint64_t d_ahi = tc::smem_desc_k_sw128(st + 0 * TC_TILE_BYTES);
+            const uint64_t d_alo = tc::smem_desc_k_sw128(st + 1 * TC_TILE_BYTES);
+            const uint64_t d_bhi = tc::smem_desc_k_sw128(st + 2 * TC_TILE_BYTES);
+            const uint64_t d_blo = tc::smem_desc_k_sw128(st + 3 * TC_TILE_BYTES);
+#pragma unroll
+            for (int k = 0; k < TC_BK / 8; ++k) {
+              const uint32_t off = (uint32_t)k * 32u;  // 8 TF32 = 32 bytes inside the swizzled 128-byte row
+              const uint32_t acc = (kb == 0 && k == 0) ? 0u : 1u;
+              tc::mma_tf32(acc_main, tc::smem_desc_advance(d_ahi, off), tc::smem_desc_advance(d_bhi, off), idesc, acc);
+              tc::mma_tf32(acc_corr, tc::smem_desc_advance(d_ahi, off), tc::smem_desc_advance(d_blo, off), idesc, acc);
+              tc::mma_tf32(acc_corr, tc::smem_desc_advance(d_alo, off), tc::smem_desc_advance(d_bhi, off), idesc, 1u);
+            }
+            tc::mma_commit(&empty[s]);  // frees the stage once these MMAs have read it
           }
-          tc::mma_commit(&empty[s]);  // frees the stage once these MMAs have read it
         }
         tc::mma_commit(&acc_full[a]);
         ++tl;
       }
     }
-  } else if (warp < 6) {
-    // ===== epilogue (warps 2..5; TMEM lane quarter = warp % 4) =====
-    const int q = warp & 3;
-    float *stg = stg_all + (warp - 2) * (32 * TC_STG_LD);
+  } else if (warp < 2 + TC_EPI_WARPS) {
+    // ===== epilogue (warps 2..9; TMEM lane quarter = warp % 4, column half = (warp - 2) / 4) =====
+    const int q = warp & 3, half = (warp - 2) >> 2;
+    const uint32_t stg = tc::smem_u32(smem + TC_RING_BYTES) + (uint32_t)(warp - 2) * 4096u;
     uint32_t tl = 0;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
       int64_t z, mb, nb, k_begin;
       int nkb;
       if (!tile_coords(tile, z, mb, nb, nkb, k_begin)) continue;
-      const uint32_t a = tl & 1u, aph = (tl >> 1) & 1u;
+      const uint32_t a = tl % ACC_SETS, aph = (tl / ACC_SETS) & 1u;
       tc::mbar_wait(&acc_full[a], aph);
+      if (threadIdx.x == 64) tc_trace(p, 3, tl, 0);
       tc::tc_fence_after();
-      const int64_t m0 = mb * TC_BM, n0 = nb * TC_BN;
+      const int64_t m0 = mb * TC_BM, n0 = nb * TC_BN + half * 64;
       const int64_t m_row = m0 + q * 32 + lane;  // the row this thread owns in the TMEM layout
-      const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16) + a * (2 * TC_BN);
+      const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16) + a * (2 * TC_BN) + (uint32_t)(half * 64);
+      float v[2][32];
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        float t[32];
+        tc::tmem_ld_32x32(lane_base + (uint32_t)(TC_BN + b * 32), v[b]);  // corrections first (smallest)
+        tc::tmem_ld_32x32(lane_base + (uint32_t)(b * 32), t);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[b][j] += t[j];
+      }
+      tc::tc_fence_before();  // this warp's share of the set is in registers: hand it back to the MMA issuer
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(&acc_empty[a]);
+      if (threadIdx.x == 64) tc_trace(p, 3, tl, 1);
       double lsum = 0.0;
       unsigned int best = 0xffffffffu;
       const unsigned int wgt = (SYMMETRIC && nb != mb) ? 2u : 1u;
-#pragma unroll 1
-      for (int c0 = 0; c0 < TC_BN; c0 += 32) {
-        float v[32], t[32];
-        tc::tmem_ld_32x32(lane_base + (uint32_t)(TC_BN + c0), v);  // corrections first (smallest)
-        tc::tmem_ld_32x32(lane_base + (uint32_t)c0, t);
 #pragma unroll
-        for (int j = 0; j < 32; ++j) v[j] += t[j];
-        if (c0 + 32 >= TC_BN) {  // last TMEM read of this set: hand it back to the MMA issuer
-          tc::tc_fence_before();
-          __syncwarp();
-          if (lane == 0) tc::mbar_arrive(&acc_empty[a]);
-        }
-        if (n0 + c0 >= p.n) continue;
+      for (int b = 0; b < 2; ++b) {
+        const int64_t nc = n0 + b * 32;
+        if (nc >= p.n) continue;
         if (EPI == EPI_HIST) {
           if (m_row < p.m) {
             const unsigned int prefix = p.g.sel->prefix, mask = p.g.sel->mask;
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
-              if (n0 + c0 + j < p.n) {
-                const unsigned int key = f32_key(v[j]);
+              if (nc + j < p.n) {
+                const unsigned int key = f32_key(v[b][j]);
                 if ((key & mask) == prefix) atomicAdd(&sh_hist[(key >> p.g.shift) & p.g.bin_mask], wgt);
               }
             }
@@ -366,8 +436,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constan
             const unsigned int base = p.g.sel->prefix;
 #pragma unroll
             for (int j = 0; j < 32; ++j) {
-              if (n0 + c0 + j < p.n) {
-                const unsigned int key = f32_key(v[j]);
+              if (nc + j < p.n) {
+                const unsigned int key = f32_key(v[b][j]);
                 if (key > base) best = min(best, key);
               }
             }
@@ -375,52 +445,73 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constan
         } else {
           __syncwarp();  // the previous block's staging reads are done
 #pragma unroll
-          for (int j = 0; j < 32; ++j) stg[lane * TC_STG_LD + j] = v[j];
+          for (int c = 0; c < 8; ++c)
+            tc::sts_f4(stg + tc_stg_off(lane, c), make_float4(v[b][4 * c], v[b][4 * c + 1], v[b][4 * c + 2], v[b][4 * c + 3]));
           __syncwarp();
-          tc_epilogue_block<EPI>(p, z, m0 + q * 32, n0 + c0, stg, lane, lsum);
+          tc_epilogue_block<EPI>(p, z, m0 + q * 32, nc, stg, lane, lsum);
         }
       }
       if (EPI == EPI_GSS) {
         lsum = warp_sum(lsum);
-        named_bar_sync(1, 128);  // the previous tile's partial has been consumed
-        if (lane == 0) red[q] = lsum;
-        named_bar_sync(1, 128);
-        if (warp == 2 && lane == 0) p.g.loss_partials[mb * tiles_n + nb] = (red[0] + red[1]) + (red[2] + red[3]);
+        named_bar_sync(1, 32 * TC_EPI_WARPS);  // the previous tile's partial has been consumed
+        if (lane == 0) red[warp - 2] = lsum;
+        named_bar_sync(1, 32 * TC_EPI_WARPS);
+        if (warp == 2 && lane == 0)
+          p.g.loss_partials[mb * tiles_n + nb] =
+              ((red[0] + red[1]) + (red[2] + red[3])) + ((red[4] + red[5]) + (red[6] + red[7]));
       }
       if (EPI == EPI_MINGT) {
 #pragma unroll
         for (int o = 16; o > 0; o >>= 1) best = min(best, __shfl_xor_sync(0xffffffffu, best, o));
         if (lane == 0 && best != 0xffffffffu) atomicMin(&p.g.sel_out->min_gt, best);
       }
+      if (threadIdx.x == 64) tc_trace(p, 3, tl, 2);
       ++tl;
     }
   } else if (RAW_A) {
-    // ===== converter warps (6..9): raw fp32 A tile -> hi (in place) + lo (neighbouring slot) =====
-    const int t = threadIdx.x - 192;  // 0..127
+    // ===== converter warps (10..13): raw fp32 A row -> TF32 hi / lo -> tensor memory =====
+    const int q = warp & 3;                      // the TMEM lane quarter this warp may touch
+    const int r = q * 32 + lane;                 // tile row owned by this thread
+    const uint32_t row_off = (uint32_t)r * 128u; // 128-byte rows; chunk j of row r sits at j ^ (r % 8) (SWIZZLE_128B)
+    const uint32_t sw = (uint32_t)(r & 7);
+    const uint32_t smem_base = tc::smem_u32(smem);
+    const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16) + A_RING_COL;
     uint32_t it = 0;
     for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
       int64_t z, mb, nb, k_begin;
       int nkb;
       if (!tile_coords(tile, z, mb, nb, nkb, k_begin)) continue;
       for (int kb = 0; kb < nkb; ++kb, ++it) {
-        const int s = it % TC_STAGES;
-        const uint32_t ph = (it / TC_STAGES) & 1u;
-        tc::mbar_wait(&full[s], ph);
-        float4 *hi4 = reinterpret_cast<float4 *>(smem + s * TC_STAGE_BYTES);
-        float4 *lo4 = reinterpret_cast<float4 *>(smem + s * TC_STAGE_BYTES + TC_TILE_BYTES);
+        const int s = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1u;
+        tc::mbar_wait(&afull[s], ph);
+        if (threadIdx.x == TC_THREADS) tc_trace(p, 2, it, 0);
+        const uint32_t src = smem_base + (uint32_t)s * STAGE_BYTES + row_off;
+        float4 x[8];
 #pragma unroll
-        for (int i = 0; i < TC_TILE_BYTES / 16 / 128; ++i) {  // the swizzle is the same in both tiles
-          const float4 x = hi4[t + i * 128];
-          float4 h, l;
-          h.x = rn_tf32(x.x); l.x = rn_tf32(x.x - h.x);
-          h.y = rn_tf32(x.y); l.y = rn_tf32(x.y - h.y);
-          h.z = rn_tf32(x.z); l.z = rn_tf32(x.z - h.z);
-          h.w = rn_tf32(x.w); l.w = rn_tf32(x.w - h.w);
-          hi4[t + i * 128] = h;
-          lo4[t + i * 128] = l;
+        for (int j = 0; j < 8; ++j) x[j] = tc::lds_f4(src + ((((uint32_t)j) ^ sw) << 4));
+        uint32_t hi[32], lo[32];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+          const float e[4] = {x[j].x, x[j].y, x[j].z, x[j].w};
+#pragma unroll
+          for (int c = 0; c < 4; ++c) {
+            const uint32_t h = tc::cvt_tf32(e[c]);
+            hi[j * 4 + c] = h;
+            lo[j * 4 + c] = tc::cvt_tf32(e[c] - __uint_as_float(h));
+          }
         }
-        tc::fence_proxy_async();
-        tc::mbar_arrive(&conv[s]);
+        tc::mbar_arrive(&aempty[s]);         // the raw tile is in registers: TMA may refill the slot
+        if (threadIdx.x == TC_THREADS) tc_trace(p, 2, it, 1);
+        tc::mbar_wait(&tempty[s], ph ^ 1u);  // the MMAs of the previous lap have read this TMEM stage
+        if (threadIdx.x == TC_THREADS) tc_trace(p, 2, it, 2);
+        tc::tc_fence_after();
+        tc::tmem_st_32x32(t_lane + (uint32_t)s * 64u, hi);
+        tc::tmem_st_32x32(t_lane + (uint32_t)s * 64u + 32u, lo);
+        tc::tmem_st_wait();
+        tc::tc_fence_before();
+        tc::mbar_arrive(&tfull[s]);
+        if (threadIdx.x == TC_THREADS) tc_trace(p, 2, it, 3);
       }
     }
   }
@@ -506,16 +597,17 @@ static int launch_gemm_tc(const float *ahi, const float *alo, const float *bhi, 
   if ((rc = make_operand_map(&mbl, blo, n, k, ldb))) return rc;
   TcParams p{};
   p.m = m; p.n = n; p.k = k; p.k_per_split = k_per_split; p.splits = splits > 0 ? splits : 1;
-  p.k_a2 = RAW_A ? k_a2 : k; p.g = g;
+  p.k_a2 = RAW_A ? k_a2 : k; p.g = g; p.trace = g_tc_trace;
+  constexpr int smem_bytes = tc_smem_bytes(EPI != EPI_HIST && EPI != EPI_MINGT);
   static bool attr_set = false;  // per template instance
   if (!attr_set) {
     GDR_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<EPI, RAW_A>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                  TC_SMEM_BYTES));
+                                  smem_bytes));
     attr_set = true;
   }
   const int64_t tiles = ceil_div<int64_t>(n, TC_BN) * ceil_div<int64_t>(m, TC_BM) * p.splits;
   const unsigned grid = (unsigned)std::min<int64_t>(tiles, kNumSMs);  // persistent: one CTA per SM walks the tiles
-  gemm_tc_kernel<EPI, RAW_A><<<grid, RAW_A ? TC_THREADS_RAW : TC_THREADS, TC_SMEM_BYTES, st>>>(ma, ml, mb, mbl, p);
+  gemm_tc_kernel<EPI, RAW_A><<<grid, RAW_A ? TC_THREADS_RAW : TC_THREADS, smem_bytes, st>>>(ma, ml, mb, mbl, p);
   GDR_LAUNCHED();
   return GDR_OK;
 }
@@ -571,6 +663,13 @@ int tc_gemm_raw_a(int epi, const float *a1, int64_t lda1, int64_t k1, const floa
 using namespace gdr;
 
 extern "C" {
+
+// Diagnostic hook: while `buf` (device, 4*128*4 int64, zeroed by the caller) is set, CTA 0 of every tensor-core GEMM
+// launch records clock64() at its pipeline hand-offs into it; nullptr switches the recording off.
+int gdr_debug_tc_trace(long long *buf) {
+  g_tc_trace = buf;
+  return GDR_OK;
+}
 
 int64_t gdr_gemm_nt_tc_workspace_bytes(int64_t m, int64_t n, int64_t k) {
   if (m < 0 || n < 0 || k <= 0) return GDR_E_BADARG;
