@@ -349,6 +349,15 @@ int gdr_linear_bwd_input_tc_f32(const float *g, const float *w, const float *e1,
   return tc_gemm_raw_a(EPI_STORE, g, d, d, nullptr, 0, 0, bhi, blo, d, n, d, q, st);
 }
 
+// TN kernel (gemm_tc_tn_kernel): one work item per SM — K ranges so that tiles * splits <= 148
+static int tn_splits_for(int64_t n, int64_t tiles, int64_t *k_per_split) {
+  int64_t s = kNumSMs / tiles;
+  if (s < 1) s = 1;
+  const int64_t per = align_up(ceil_div<int64_t>(n > 0 ? n : 1, s), TC_K_ALIGN);
+  *k_per_split = per;
+  return (int)ceil_div<int64_t>(n > 0 ? n : 1, per);
+}
+
 static int tc_splits_for(int64_t n, int64_t d, int64_t *k_per_split) {
   const int64_t tiles = ceil_div<int64_t>(d, 128) * ceil_div<int64_t>(d, 128);
   int64_t s = ceil_div<int64_t>(2 * kNumSMs, tiles);                  // ~2 CTAs per SM in total
@@ -364,7 +373,10 @@ int64_t gdr_linear_bwd_weight_tc_workspace_bytes(int64_t n, int64_t d) {
   const int64_t splits = tc_splits_for(n, d, &per);
   const int64_t ldt = align_up(n > 0 ? n : 1, 4);
   const int64_t cs_blocks = ceil_div<int64_t>(n > 0 ? n : 1, CS_ROWS);
-  return 4 * align_up(d * ldt * 4, 256) + align_up(splits * d * d * 4, 256) + align_up(cs_blocks * d * 4, 256) + 1024;
+  int64_t tn_per;
+  const int64_t tn = tn_splits_for(n, ceil_div<int64_t>(d, 128) * ceil_div<int64_t>(d, 128), &tn_per);
+  return 4 * align_up(d * ldt * 4, 256) + align_up(std::max(splits, tn) * d * d * 4, 256) +
+         align_up(std::max(cs_blocks, tn) * d * 4, 256) + 1024;
 }
 
 int gdr_linear_bwd_weight_tc_f32(const float *g, const float *a, int64_t n, int64_t d, int accumulate, float *dw,
@@ -381,28 +393,18 @@ int gdr_linear_bwd_weight_tc_f32(const float *g, const float *a, int64_t n, int6
     }
     return GDR_OK;
   }
+  // raw operands straight into the TN kernel: no transposed copies, column sums from the A converter
   int64_t per;
-  const int splits = tc_splits_for(n, d, &per);
-  const int64_t ldt = align_up(n, 4);
-  const int64_t cs_blocks = ceil_div<int64_t>(n, CS_ROWS);
-  Carver cv(workspace);
-  float *ghi = cv.take<float>(d * ldt), *glo = cv.take<float>(d * ldt);
-  float *ahi = cv.take<float>(d * ldt), *alo = cv.take<float>(d * ldt);
-  float *part = cv.take<float>((int64_t)splits * d * d);
-  float *cpart = cv.take<float>(cs_blocks * d);
   int rc;
-  if ((rc = tc_split_transpose(g, d, n, d, ldt, ghi, glo, st))) return rc;   // A(m=out, k=node) = Gᵀ
-  if ((rc = tc_split_transpose(a, d, n, d, ldt, ahi, alo, st))) return rc;   // B(n=in,  k=node) = Aᵀ
-  GemmParams q{};
-  q.c = part; q.ldc = d;
-  if ((rc = tc_gemm(EPI_SPLITK, ghi, glo, ahi, alo, d, d, n, ldt, ldt, per, splits, q, st))) return rc;
-  splitk_reduce_kernel<<<(unsigned)ceil_div<int64_t>(d * d, 32), 256, 0, st>>>(part, splits, d * d, accumulate, dw);
+  const int tn = tn_splits_for(n, ceil_div<int64_t>(d, 128) * ceil_div<int64_t>(d, 128), &per);
+  Carver cv(workspace);
+  float *part = cv.take<float>((int64_t)tn * d * d);
+  float *cpart = cv.take<float>((int64_t)tn * d);
+  if ((rc = tc_gemm_tn_splitk(g, d, d, a, d, d, nullptr, 0, 0, n, per, tn, part, db ? cpart : nullptr, st))) return rc;
+  splitk_reduce_kernel<<<(unsigned)ceil_div<int64_t>(d * d, 32), 256, 0, st>>>(part, tn, d * d, accumulate, dw);
   GDR_LAUNCHED();
   if (db) {
-    colsum_partial_kernel<<<(unsigned)cs_blocks, 256, 0, st>>>(g, n, d, cpart);
-    GDR_LAUNCHED();
-    splitk_reduce_kernel<<<(unsigned)ceil_div<int64_t>(d, 32), 256, 0, st>>>(cpart, (int)cs_blocks, d, accumulate,
-                                                                             db);
+    splitk_reduce_kernel<<<(unsigned)ceil_div<int64_t>(d, 32), 256, 0, st>>>(cpart, tn, d, accumulate, db);
     GDR_LAUNCHED();
   }
   return GDR_OK;
@@ -420,8 +422,10 @@ int64_t gdr_linear_bwd_weight2_tc_workspace_bytes(int64_t n, int64_t d) {
   const int64_t splits = ceil_div<int64_t>(n > 0 ? n : 1, per);
   const int64_t ldt = align_up(n > 0 ? n : 1, 4);
   const int64_t cs_blocks = ceil_div<int64_t>(n > 0 ? n : 1, CS_ROWS);
-  return 2 * align_up(d * ldt * 4, 256) + 2 * align_up(2 * d * ldt * 4, 256) + align_up(splits * d * 2 * d * 4, 256) +
-         align_up(cs_blocks * d * 4, 256) + 1024;
+  int64_t tn_per;
+  const int64_t tn = tn_splits_for(n, tiles, &tn_per);
+  return 2 * align_up(d * ldt * 4, 256) + 2 * align_up(2 * d * ldt * 4, 256) +
+         align_up(std::max(splits, tn) * d * 2 * d * 4, 256) + align_up(std::max(cs_blocks, tn) * d * 4, 256) + 1024;
 }
 
 int gdr_linear_bwd_weight2_tc_f32(const float *g, const float *a1, const float *a2, int64_t n, int64_t d,
@@ -443,6 +447,21 @@ int gdr_linear_bwd_weight2_tc_f32(const float *g, const float *a1, const float *
     return GDR_OK;
   }
   const int64_t tiles = ceil_div<int64_t>(d, 128) * ceil_div<int64_t>(2 * d, 128);
+  int rc;
+  if (d % 128 == 0) {  // an N tile never straddles A1 | A2: raw operands straight into the TN kernel
+    int64_t tn_per;
+    const int tn = tn_splits_for(n, tiles, &tn_per);
+    Carver cv(workspace);
+    float *part = cv.take<float>((int64_t)tn * d * 2 * d);
+    float *cpart = cv.take<float>((int64_t)tn * d);
+    if ((rc = tc_gemm_tn_splitk(g, d, d, a1, d, d, a2, d, d, n, tn_per, tn, part, cpart, st))) return rc;
+    splitk_reduce2_kernel<<<(unsigned)ceil_div<int64_t>(d * 2 * d, 32), 256, 0, st>>>(part, tn, d, d, accumulate, 0, dw1,
+                                                                                   dw2);
+    GDR_LAUNCHED();
+    splitk_reduce2_kernel<<<(unsigned)ceil_div<int64_t>(d, 32), 256, 0, st>>>(cpart, tn, 1, d, accumulate, 1, db1, db2);
+    GDR_LAUNCHED();
+    return GDR_OK;
+  }
   int64_t per = align_up(ceil_div<int64_t>(n, ceil_div<int64_t>(2 * kNumSMs, tiles)), TC_K_ALIGN);
   if (per < 4 * TC_K_ALIGN) per = 4 * TC_K_ALIGN;
   const int splits = (int)ceil_div<int64_t>(n, per);
@@ -453,7 +472,6 @@ int gdr_linear_bwd_weight2_tc_f32(const float *g, const float *a1, const float *
   float *ahi = cv.take<float>(2 * d * ldt), *alo = cv.take<float>(2 * d * ldt);
   float *part = cv.take<float>((int64_t)splits * d * 2 * d);
   float *cpart = cv.take<float>(cs_blocks * d);
-  int rc;
   if ((rc = tc_split_transpose(g, d, n, d, ldt, ghi, glo, st))) return rc;                         // A(m=out, k=node)
   if ((rc = tc_split_transpose(a1, d, n, d, ldt, ahi, alo, st))) return rc;                        // B rows 0..d-1
   if ((rc = tc_split_transpose(a2, d, n, d, ldt, ahi + d * ldt, alo + d * ldt, st))) return rc;    // B rows d..2d-1

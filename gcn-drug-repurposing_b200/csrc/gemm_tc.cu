@@ -41,6 +41,7 @@ struct TcParams {
   int64_t splits;          // EPI_SPLITK: number of K ranges (tiles = tiles_m * tiles_n * splits); otherwise 1
   int64_t k_a2;            // RAW_A: columns [k_a2, k) of A come from the second raw source (k_a2 % TC_BK == 0)
   GemmParams g;            // epilogue operands, same meaning as in gemm_simt.cuh (a/b/lda/ldb unused)
+  float *colsum_part;      // TN form: column sums of the A source per K range, [splits][m] (nullptr: not wanted)
   long long *trace;        // diagnostic: CTA 0 records clock64() at the pipeline hand-offs (gdr_debug_tc_trace)
 };
 
@@ -530,6 +531,266 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constan
   }
 }
 
+// ---- TN form: C[M,N] = Aᵀ·B with A [K, M] and B [K, N] row-major (the weight gradient dW = Gᵀ·[A1 | A2],
+// modules/model.py:165,170 under autograd: the reduction runs over the NODE dimension, so both operands are
+// "MN-major").  Same pipeline as gemm_tc_kernel<., RAW_A>, both operands raw fp32:
+//   A: TMA box [32 k x 128 m], unswizzled; converter thread m reads its COLUMN (32 conflict-free LDS.32), splits it
+//      and stores it as its TMEM lane — the transposition costs nothing; its fp64 running sum is the column sum of
+//      the A source (db = colsum(G)) for free.
+//   B: four TMA boxes [32 k x 32 n], SWIZZLE_128B_ATOM_32B = the canonical MN-major TF32 UMMA layout; four more warps split the
+//      tile in place (hi) and into the neighbouring slot (lo); the MMAs read it through an MN-major descriptor.
+// Split-K: a work item is (m tile, n tile, K range); partial tiles go to part[z][M][N], reduced by
+// splitk_reduce2_kernel in a fixed order (deterministic).  This replaces three transposing split kernels, the
+// pre-split GEMM and the column-sum kernel of the round-1 path.
+constexpr int TN_THREADS = TC_THREADS + 256;  // + 4 A-converter warps + 4 B-converter warps
+
+__global__ void __launch_bounds__(TN_THREADS, 1)
+gemm_tc_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_constant__ CUtensorMap map_b1,
+                  const __grid_constant__ CUtensorMap map_b2, const TcParams p) {
+  constexpr int STAGES = TC_STAGES_RAW;
+  constexpr int STAGE_BYTES = 3 * TC_TILE_BYTES;  // A raw | B raw -> B_hi | B_lo
+  constexpr uint32_t A_RING_COL = 2 * TC_BN;
+
+  extern __shared__ unsigned char tc_smem_raw[];
+  unsigned char *smem = tc_smem_raw + ((1024u - (tc::smem_u32(tc_smem_raw) & 1023u)) & 1023u);
+  uint64_t *full = reinterpret_cast<uint64_t *>(smem + TC_RING_BYTES + TC_STG_BYTES);  // raw B tile landed
+  uint64_t *empty = full + 4;    // B stage consumed by the MMAs
+  uint64_t *afull = empty + 4;   // raw A tile landed
+  uint64_t *aempty = afull + 4;  // raw A tile read by the A converter
+  uint64_t *tfull = aempty + 4;  // A hi/lo in tensor memory
+  uint64_t *tempty = tfull + 4;  // the MMAs have read that TMEM stage
+  uint64_t *bconv = tempty + 4;  // B hi/lo written to shared memory
+  uint64_t *acc_full = bconv + 4;
+  uint64_t *acc_empty = acc_full + 1;
+  uint32_t *tmem_slot = reinterpret_cast<uint32_t *>(acc_empty + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int64_t tiles_n = ceil_div<int64_t>(p.n, TC_BN), tiles_m = ceil_div<int64_t>(p.m, TC_BM);
+  const int64_t tiles_mn = tiles_m * tiles_n;
+  const int64_t n_tiles = tiles_mn * p.splits;
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < 4; ++s) {
+      tc::mbar_init(&full[s], 1);
+      tc::mbar_init(&empty[s], 1);
+      tc::mbar_init(&afull[s], 1);
+      tc::mbar_init(&aempty[s], 128);
+      tc::mbar_init(&tfull[s], 128);
+      tc::mbar_init(&tempty[s], 1);
+      tc::mbar_init(&bconv[s], 128);
+    }
+    tc::mbar_init(acc_full, 1);
+    tc::mbar_init(acc_empty, TC_EPI_WARPS);
+    tc::mbar_fence_init();
+    tc::tma_prefetch_desc(&map_a);
+    tc::tma_prefetch_desc(&map_b1);
+    tc::tma_prefetch_desc(&map_b2);
+  }
+  if (warp == 1) tc::tmem_alloc(tmem_slot, 512);
+  tc::tc_fence_before();
+  __syncthreads();
+  tc::tc_fence_after();
+  const uint32_t tmem = *tmem_slot;
+
+  auto tile_coords = [&](int64_t tile, int64_t &z, int64_t &mb, int64_t &nb, int &nkb, int64_t &k_begin) {
+    z = tile / tiles_mn;
+    const int64_t r = tile - z * tiles_mn;
+    mb = r / tiles_n;
+    nb = r - mb * tiles_n;
+    k_begin = z * p.k_per_split;
+    const int64_t k_end = min(p.k, k_begin + p.k_per_split);
+    nkb = (int)((k_end - k_begin + TC_BK - 1) / TC_BK);
+  };
+
+  if (warp == 0) {
+    // ===== TMA producer =====
+    if (lane == 0) {
+      uint32_t it = 0;
+      for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        int64_t z, mb, nb, k_begin;
+        int nkb;
+        tile_coords(tile, z, mb, nb, nkb, k_begin);
+        const int32_t m0 = (int32_t)(mb * TC_BM);
+        int32_t n0 = (int32_t)(nb * TC_BN);
+        const CUtensorMap *mapb = &map_b1;
+        if (n0 >= p.k_a2) {  // k_a2 = width of the first B source (a multiple of TC_BN)
+          mapb = &map_b2;
+          n0 -= (int32_t)p.k_a2;
+        }
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1u;
+          unsigned char *st = smem + s * STAGE_BYTES;
+          const int32_t kc = (int32_t)(k_begin + (int64_t)kb * TC_BK);
+          tc::mbar_wait(&aempty[s], ph ^ 1u);
+          tc::mbar_expect_tx(&afull[s], TC_TILE_BYTES);
+          tc::tma_load_2d(st, &map_a, &afull[s], m0, kc);
+          tc::mbar_wait(&empty[s], ph ^ 1u);
+          tc::mbar_expect_tx(&full[s], TC_TILE_BYTES);
+#pragma unroll
+          for (int j = 0; j < 4; ++j)
+            tc::tma_load_2d(st + TC_TILE_BYTES + j * 4096, mapb, &full[s], n0 + 32 * j, kc);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===== MMA issuer =====
+    if (lane == 0) {
+      constexpr uint32_t idesc = tc::idesc_tf32_bmn(TC_BM, TC_BN), idesc2 = tc::idesc_tf32_bmn(TC_BM, 2 * TC_BN);
+      uint32_t it = 0, tl = 0;
+      for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        int64_t z, mb, nb, k_begin;
+        int nkb;
+        tile_coords(tile, z, mb, nb, nkb, k_begin);
+        tc::mbar_wait(acc_empty, (tl & 1u) ^ 1u);
+        tc::tc_fence_after();
+        const uint32_t acc_main = tmem, acc_corr = tmem + TC_BN;
+        for (int kb = 0; kb < nkb; ++kb, ++it) {
+          const int s = it % STAGES;
+          const uint32_t ph = (it / STAGES) & 1u;
+          unsigned char *st = smem + s * STAGE_BYTES;
+          tc::mbar_wait(&bconv[s], ph);
+          tc::mbar_wait(&tfull[s], ph);
+          tc::tc_fence_after();
+          const uint32_t t_hi = tmem + A_RING_COL + (uint32_t)s * 64u, t_lo = t_hi + 32u;
+          const uint64_t d_bhi = tc::smem_desc_mn_sw128_32b(st + TC_TILE_BYTES);  // B_lo = the next four 4 KB blocks
+#pragma unroll
+          for (int k = 0; k < TC_BK / 8; ++k) {
+            const uint32_t off = (uint32_t)k * 1024u, col = (uint32_t)k * 8u;  // 8 K-rows of 128 bytes
+            const uint32_t acc = (kb == 0 && k == 0) ? 0u : 1u;
+            tc::mma_tf32_ts(acc_main, t_hi + col, tc::smem_desc_advance(d_bhi, off), idesc2, acc);
+            tc::mma_tf32_ts(acc_corr, t_lo + col, tc::smem_desc_advance(d_bhi, off), idesc, 1u);
+          }
+          tc::mma_commit(&empty[s]);
+          tc::mma_commit(&tempty[s]);
+        }
+        tc::mma_commit(acc_full);
+        ++tl;
+      }
+    }
+  } else if (warp < 2 + TC_EPI_WARPS) {
+    // ===== epilogue: partial tile -> part[z][M][N] =====
+    const int q = warp & 3, half = (warp - 2) >> 2;
+    const uint32_t stg = tc::smem_u32(smem + TC_RING_BYTES) + (uint32_t)(warp - 2) * 4096u;
+    uint32_t tl = 0;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      int64_t z, mb, nb, k_begin;
+      int nkb;
+      tile_coords(tile, z, mb, nb, nkb, k_begin);
+      tc::mbar_wait(acc_full, tl & 1u);
+      tc::tc_fence_after();
+      const int64_t m0 = mb * TC_BM, n0 = nb * TC_BN + half * 64;
+      const uint32_t lane_base = tmem + ((uint32_t)(q * 32) << 16) + (uint32_t)(half * 64);
+      float v[2][32];
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        float t[32];
+        tc::tmem_ld_32x32(lane_base + (uint32_t)(TC_BN + b * 32), v[b]);
+        tc::tmem_ld_32x32(lane_base + (uint32_t)(b * 32), t);
+#pragma unroll
+        for (int j = 0; j < 32; ++j) v[b][j] += t[j];
+      }
+      tc::tc_fence_before();
+      __syncwarp();
+      if (lane == 0) tc::mbar_arrive(acc_empty);
+      double lsum = 0.0;
+#pragma unroll
+      for (int b = 0; b < 2; ++b) {
+        const int64_t nc = n0 + b * 32;
+        if (nc >= p.n) continue;
+        __syncwarp();
+#pragma unroll
+        for (int c = 0; c < 8; ++c)
+          tc::sts_f4(stg + tc_stg_off(lane, c), make_float4(v[b][4 * c], v[b][4 * c + 1], v[b][4 * c + 2], v[b][4 * c + 3]));
+        __syncwarp();
+        tc_epilogue_block<EPI_SPLITK>(p, z, m0 + q * 32, nc, stg, lane, lsum);
+      }
+      ++tl;
+    }
+  } else if (warp < 2 + TC_EPI_WARPS + 4) {
+    // ===== A converter (warps 10..13): column m of the raw [32 k x 128 m] tile -> TMEM lane m =====
+    const int q = warp & 3;
+    const int m = q * 32 + lane;
+    const uint32_t smem_base = tc::smem_u32(smem) + (uint32_t)m * 4u;
+    const uint32_t t_lane = tmem + ((uint32_t)(q * 32) << 16) + A_RING_COL;
+    uint32_t it = 0;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      int64_t z, mb, nb, k_begin;
+      int nkb;
+      tile_coords(tile, z, mb, nb, nkb, k_begin);
+      double csum = 0.0;
+      for (int kb = 0; kb < nkb; ++kb, ++it) {
+        const int s = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1u;
+        tc::mbar_wait(&afull[s], ph);
+        const uint32_t src = smem_base + (uint32_t)s * STAGE_BYTES;
+        float x[32];
+#pragma unroll
+        for (int k = 0; k < 32; ++k) x[k] = tc::lds_f32(src + (uint32_t)k * 512u);
+#pragma unroll
+        for (int k = 0; k < 32; ++k) csum += (double)x[k];
+        tc::mbar_arrive(&aempty[s]);
+        tc::mbar_wait(&tempty[s], ph ^ 1u);
+        tc::tc_fence_after();
+#pragma unroll
+        for (int h = 0; h < 2; ++h) {
+          uint32_t hi[16], lo[16];
+#pragma unroll
+          for (int c = 0; c < 16; ++c) {
+            hi[c] = tc::cvt_tf32(x[h * 16 + c]);
+            lo[c] = tc::cvt_tf32(x[h * 16 + c] - __uint_as_float(hi[c]));
+          }
+          tc::tmem_st_32x16(t_lane + (uint32_t)s * 64u + (uint32_t)h * 16u, hi);
+          tc::tmem_st_32x16(t_lane + (uint32_t)s * 64u + 32u + (uint32_t)h * 16u, lo);
+        }
+        tc::tmem_st_wait();
+        tc::tc_fence_before();
+        tc::mbar_arrive(&tfull[s]);
+      }
+      if (p.colsum_part != nullptr && nb == 0 && mb * TC_BM + m < p.m)
+        p.colsum_part[z * p.m + mb * TC_BM + m] = (float)csum;
+    }
+  } else {
+    // ===== B converter (warps 14..17): raw tile -> hi in place, lo in the neighbouring slot (same swizzle) =====
+    const uint32_t t = threadIdx.x - (TC_THREADS + 128);
+    const uint32_t smem_base = tc::smem_u32(smem) + TC_TILE_BYTES + t * 16u;
+    uint32_t it = 0;
+    for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+      int64_t z, mb, nb, k_begin;
+      int nkb;
+      tile_coords(tile, z, mb, nb, nkb, k_begin);
+      for (int kb = 0; kb < nkb; ++kb, ++it) {
+        const int s = it % STAGES;
+        const uint32_t ph = (it / STAGES) & 1u;
+        tc::mbar_wait(&full[s], ph);
+        const uint32_t src = smem_base + (uint32_t)s * STAGE_BYTES;
+        float4 x[8];
+#pragma unroll
+        for (int i = 0; i < 8; ++i) x[i] = tc::lds_f4(src + (uint32_t)i * 2048u);
+#pragma unroll
+        for (int i = 0; i < 8; ++i) {
+          float4 h, l;
+          h.x = __uint_as_float(tc::cvt_tf32(x[i].x)); l.x = __uint_as_float(tc::cvt_tf32(x[i].x - h.x));
+          h.y = __uint_as_float(tc::cvt_tf32(x[i].y)); l.y = __uint_as_float(tc::cvt_tf32(x[i].y - h.y));
+          h.z = __uint_as_float(tc::cvt_tf32(x[i].z)); l.z = __uint_as_float(tc::cvt_tf32(x[i].z - h.z));
+          h.w = __uint_as_float(tc::cvt_tf32(x[i].w)); l.w = __uint_as_float(tc::cvt_tf32(x[i].w - h.w));
+          tc::sts_f4(src + (uint32_t)i * 2048u, h);
+          tc::sts_f4(src + (uint32_t)i * 2048u + TC_TILE_BYTES, l);
+        }
+        tc::fence_proxy_async();
+        tc::mbar_arrive(&bconv[s]);
+      }
+    }
+  }
+
+  tc::tc_fence_before();
+  __syncthreads();
+  if (warp == 1) {
+    tc::tc_fence_after();
+    tc::tmem_dealloc(tmem, 512);
+  }
+}
+
 // ---- host side ---------------------------------------------------------------------------------------
 typedef CUresult (*EncodeTiledFn)(CUtensorMap *, CUtensorMapDataType, cuuint32_t, void *, const cuuint64_t *,
                                   const cuuint64_t *, const cuuint32_t *, const cuuint32_t *, CUtensorMapInterleave,
@@ -566,6 +827,58 @@ static int make_operand_map(CUtensorMap *map, const float *base, int64_t rows, i
     set_error("gemm_tc: cuTensorMapEncodeTiled failed (%d)", (int)r);
     return GDR_E_INTERNAL;
   }
+  return GDR_OK;
+}
+
+// [k_rows, width] fp32 row-major -> boxes of box_w columns x 32 rows (the reduction index is the slow one)
+static int make_mn_map(CUtensorMap *map, const float *base, int64_t k_rows, int64_t width, int64_t ld, int box_w,
+                       bool swizzle) {
+  EncodeTiledFn enc = encode_tiled_fn();
+  if (!enc) {
+    set_error("gemm_tc: cuTensorMapEncodeTiled is not available from this driver");
+    return GDR_E_INTERNAL;
+  }
+  const cuuint64_t gdim[2] = {(cuuint64_t)width, (cuuint64_t)k_rows};
+  const cuuint64_t gstride[1] = {(cuuint64_t)ld * 4u};
+  const cuuint32_t box[2] = {(cuuint32_t)box_w, (cuuint32_t)TC_BK};
+  const cuuint32_t estr[2] = {1u, 1u};
+  const CUresult r = enc(map, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<float *>(base), gdim, gstride, box, estr,
+                         CU_TENSOR_MAP_INTERLEAVE_NONE, swizzle ? CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B : CU_TENSOR_MAP_SWIZZLE_NONE,
+                         CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) {
+    set_error("gemm_tc: cuTensorMapEncodeTiled (MN-major operand) failed (%d)", (int)r);
+    return GDR_E_INTERNAL;
+  }
+  return GDR_OK;
+}
+
+// part[z][m][n1 + n2] = A[k range z, 0:m]ᵀ · [B1 | B2][k range z, :]; colsum_part[z][m] = column sums of A (optional)
+int tc_gemm_tn_splitk(const float *a, int64_t lda, int64_t m, const float *b1, int64_t ldb1, int64_t n1,
+                      const float *b2, int64_t ldb2, int64_t n2, int64_t k, int64_t k_per_split, int splits,
+                      float *part, float *colsum_part, cudaStream_t st) {
+  if ((lda % 4) || (ldb1 % 4) || (ldb2 % 4) || (((uintptr_t)a | (uintptr_t)b1 | (uintptr_t)b2) & 15) ||
+      (n2 > 0 && (n1 % TC_BN)) || ((n1 + n2) % 4) || (k_per_split % TC_BK)) {
+    set_error("gemm_tc_tn: operands must be 16-byte aligned, leading dimensions %% 4 == 0, first N source %% %d == 0", TC_BN);
+    return GDR_E_SHAPE;
+  }
+  int rc;
+  CUtensorMap ma, mb1, mb2;
+  if ((rc = make_mn_map(&ma, a, k, m, lda, TC_BM, false))) return rc;
+  if ((rc = make_mn_map(&mb1, b1, k, n1, ldb1, 32, true))) return rc;
+  if ((rc = make_mn_map(&mb2, n2 > 0 ? b2 : b1, k, n2 > 0 ? n2 : n1, n2 > 0 ? ldb2 : ldb1, 32, true))) return rc;
+  TcParams p{};
+  p.m = m; p.n = n1 + n2; p.k = k; p.k_per_split = k_per_split; p.splits = splits; p.k_a2 = n1;
+  p.g.c = part; p.g.ldc = n1 + n2; p.colsum_part = colsum_part; p.trace = nullptr;
+  constexpr int smem_bytes = tc_smem_bytes(true);
+  static bool attr_set = false;
+  if (!attr_set) {
+    GDR_CUDA(cudaFuncSetAttribute(gemm_tc_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
+    attr_set = true;
+  }
+  const int64_t tiles = ceil_div<int64_t>(p.n, TC_BN) * ceil_div<int64_t>(m, TC_BM) * splits;
+  const unsigned grid = (unsigned)std::min<int64_t>(tiles, kNumSMs);
+  gemm_tc_tn_kernel<<<grid, TN_THREADS, smem_bytes, st>>>(ma, mb1, mb2, p);
+  GDR_LAUNCHED();
   return GDR_OK;
 }
 

@@ -22,6 +22,13 @@ int tc_gemm_raw_a(int epi, const float *a1, int64_t lda1, int64_t k1, const floa
                   const float *bhi, const float *blo, int64_t ldb, int64_t m, int64_t n, const GemmParams &g,
                   cudaStream_t st);
 
+// TN form on raw operands: part[z][m][n1 + n2] = A[K range z, 0:m]ᵀ · [B1 | B2][K range z, :], A [k, m] and B1/B2
+// [k, n1] / [k, n2] row-major (n1, n2 multiples of 128; n2 == 0: one source), K ranges of k_per_split rows
+// (a multiple of 32).  colsum_part[z][m] (optional) receives the column sums of A over each K range.
+int tc_gemm_tn_splitk(const float *a, int64_t lda, int64_t m, const float *b1, int64_t ldb1, int64_t n1,
+                      const float *b2, int64_t ldb2, int64_t n2, int64_t k, int64_t k_per_split, int splits,
+                      float *part, float *colsum_part, cudaStream_t st);
+
 constexpr int TC_K_ALIGN = 32;  // split-K ranges must be multiples of the 32-column TMA box
 
 }  // namespace gdr

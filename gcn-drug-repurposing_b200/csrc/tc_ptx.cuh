@@ -123,6 +123,14 @@ __device__ __forceinline__ void tmem_st_32x32(uint32_t taddr, const uint32_t (&r
       "r"(r[28]), "r"(r[29]), "r"(r[30]), "r"(r[31])
       : "memory");
 }
+__device__ __forceinline__ void tmem_st_32x16(uint32_t taddr, const uint32_t (&r)[16]) {
+  asm volatile(
+      "tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], "
+      "{%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+      "r"(r[0]), "r"(r[1]), "r"(r[2]), "r"(r[3]), "r"(r[4]), "r"(r[5]), "r"(r[6]), "r"(r[7]), "r"(r[8]), "r"(r[9]),
+      "r"(r[10]), "r"(r[11]), "r"(r[12]), "r"(r[13]), "r"(r[14]), "r"(r[15])
+      : "memory");
+}
 __device__ __forceinline__ void tmem_st_wait() { asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory"); }
 
 // ---- shared-memory access by 32-bit shared address (always LDS / STS, never the generic path) ----
@@ -161,6 +169,23 @@ __device__ __forceinline__ uint64_t smem_desc_k_sw128(const void *tile) {
   d |= (uint64_t)2u << 61;            // SWIZZLE_128B
   return d;
 }
+// MN-major TF32 operand tile (the M/N index is contiguous in memory, K is the slow index).  For 32-bit MN-major
+// operands the only swizzled layout tcgen05 accepts is "128B swizzle with 32-byte atoms" (cute
+// UMMA::Layout_MN_SW128_32B_Atom, descriptor layout type 1; TMA: CU_TENSOR_MAP_SWIZZLE_128B_ATOM_32B): rows of
+// 128 bytes = 32 fp32 of M/N, the 32-byte chunk index XORed with (K-row % 4).  The tile is a row of 4 KB blocks, one
+// per 32 fp32 of M/N, each block = 32 K-rows as TMA writes a [32 k x 32 mn] box.  Canonical form
+// ((8,n),(4,k)):((1,LBO),(8,SBO)) in 16-byte units: LBO = distance between 32-element M/N groups (4096), SBO =
+// distance between groups of 4 K-rows (512).  One TF32 MMA consumes 8 K-rows: advance the start by 1024 bytes per step.
+// (The plain SWIZZLE_128B MN-major descriptor is accepted for kind::tf32 but multiplies by zeros — measured.)
+__device__ __forceinline__ uint64_t smem_desc_mn_sw128_32b(const void *tile) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_u32(tile) >> 4) & 0x3fffu);
+  d |= (uint64_t)(4096u >> 4) << 16;
+  d |= (uint64_t)(512u >> 4) << 32;
+  d |= (uint64_t)1u << 46;
+  d |= (uint64_t)1u << 61;  // SWIZZLE_128B_BASE32B
+  return d;
+}
 // advance inside the 128-byte swizzle row by `bytes` (one UMMA_K step of TF32 = 8 elements = 32 bytes)
 __device__ __forceinline__ uint64_t smem_desc_advance(uint64_t d, uint32_t bytes) { return d + (uint64_t)(bytes >> 4); }
 
@@ -169,6 +194,8 @@ __device__ __forceinline__ uint64_t smem_desc_advance(uint64_t d, uint32_t bytes
 __host__ __device__ constexpr uint32_t idesc_tf32(int m, int n) {
   return (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(n >> 3) << 17) | ((uint32_t)(m >> 4) << 24);
 }
+// the same with B MN-major (b_major, bit 16)
+__host__ __device__ constexpr uint32_t idesc_tf32_bmn(int m, int n) { return idesc_tf32(m, n) | (1u << 16); }
 
 }  // namespace tc
 }  // namespace gdr
