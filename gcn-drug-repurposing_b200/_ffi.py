@@ -73,6 +73,8 @@ _SIGNATURES = {
     "gdr_gram_percentile_workspace_bytes": (c_i64, [c_i64, c_i64]),
     "gdr_gram_percentile_f32": (c_i32, [c_ptr, c_i64, c_i64, c_f64, ctypes.POINTER(c_f32), c_ptr, c_i64, c_ptr]),
     "gdr_gram_topk_f64": (c_i32, [c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr]),
+    "gdr_gram_topk_tc_workspace_bytes": (c_i64, [c_i64, c_i64, c_i64]),
+    "gdr_gram_topk_tc_f64": (c_i32, [c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_ptr]),
     "gdr_text_savetxt_bytes": (c_i64, [c_i64, c_i64]),
     "gdr_text_savetxt_e18": (c_i64, [c_ptr, c_i64, c_i64, c_i32, ctypes.c_char_p, c_i64, c_i32]),
     "gdr_text_parse_embs": (c_i64, [ctypes.c_char_p, c_i64, c_i32, c_ptr, c_i64, c_ptr, c_ptr,

@@ -50,6 +50,7 @@ __device__ __forceinline__ void tc_trace(const TcParams &p, int role, uint32_t i
   if (p.trace != nullptr && blockIdx.x == 0 && idx < 128u) p.trace[(role * 128 + (int)idx) * 4 + ev] = clock64();
 }
 static long long *g_tc_trace = nullptr;
+long long *tc_trace_buffer() { return g_tc_trace; }
 
 // ---- operand split ---------------------------------------------------------------------------------
 __device__ __forceinline__ float rn_tf32(float x) {
@@ -288,8 +289,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constan
   };
 
   if (warp == 0) {
-    // ===== TMA producer =====
-    if (lane == 0) {
+    // ===== TMA producer: the whole warp walks the loop, one elected lane issues (tc::elect_one) =====
+    {
       uint32_t it = 0;
       for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         int64_t z, mb, nb, k_begin;
@@ -303,32 +304,41 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constan
           const int32_t kc = (int32_t)(k_begin + (int64_t)kb * TC_BK);
           if (RAW_A) {
             tc::mbar_wait(&aempty[s], ph ^ 1u);  // first lap passes immediately
-            tc_trace(p, 0, it, 0);
-            tc::mbar_expect_tx(&afull[s], TC_TILE_BYTES);
-            if (kc < p.k_a2)
-              tc::tma_load_2d(st, &map_ahi, &afull[s], kc, m0);
-            else
-              tc::tma_load_2d(st, &map_alo, &afull[s], kc - (int32_t)p.k_a2, m0);
+            if (lane == 0) tc_trace(p, 0, it, 0);
+            if (tc::elect_one()) {
+              tc::mbar_expect_tx(&afull[s], TC_TILE_BYTES);
+              if (kc < p.k_a2)
+                tc::tma_load_2d(st, &map_ahi, &afull[s], kc, m0);
+              else
+                tc::tma_load_2d(st, &map_alo, &afull[s], kc - (int32_t)p.k_a2, m0);
+            }
+            __syncwarp();
             tc::mbar_wait(&empty[s], ph ^ 1u);
-            tc_trace(p, 0, it, 1);
-            tc::mbar_expect_tx(&full[s], 2 * TC_TILE_BYTES);
-            tc::tma_load_2d(st + 1 * TC_TILE_BYTES, &map_bhi, &full[s], kc, n0);
-            tc::tma_load_2d(st + 2 * TC_TILE_BYTES, &map_blo, &full[s], kc, n0);
-            tc_trace(p, 0, it, 2);
+            if (lane == 0) tc_trace(p, 0, it, 1);
+            if (tc::elect_one()) {
+              tc::mbar_expect_tx(&full[s], 2 * TC_TILE_BYTES);
+              tc::tma_load_2d(st + 1 * TC_TILE_BYTES, &map_bhi, &full[s], kc, n0);
+              tc::tma_load_2d(st + 2 * TC_TILE_BYTES, &map_blo, &full[s], kc, n0);
+            }
+            __syncwarp();
+            if (lane == 0) tc_trace(p, 0, it, 2);
           } else {
             tc::mbar_wait(&empty[s], ph ^ 1u);
-            tc::mbar_expect_tx(&full[s], 4 * TC_TILE_BYTES);
-            tc::tma_load_2d(st + 0 * TC_TILE_BYTES, &map_ahi, &full[s], kc, m0);
-            tc::tma_load_2d(st + 1 * TC_TILE_BYTES, &map_alo, &full[s], kc, m0);
-            tc::tma_load_2d(st + 2 * TC_TILE_BYTES, &map_bhi, &full[s], kc, n0);
-            tc::tma_load_2d(st + 3 * TC_TILE_BYTES, &map_blo, &full[s], kc, n0);
+            if (tc::elect_one()) {
+              tc::mbar_expect_tx(&full[s], 4 * TC_TILE_BYTES);
+              tc::tma_load_2d(st + 0 * TC_TILE_BYTES, &map_ahi, &full[s], kc, m0);
+              tc::tma_load_2d(st + 1 * TC_TILE_BYTES, &map_alo, &full[s], kc, m0);
+              tc::tma_load_2d(st + 2 * TC_TILE_BYTES, &map_bhi, &full[s], kc, n0);
+              tc::tma_load_2d(st + 3 * TC_TILE_BYTES, &map_blo, &full[s], kc, n0);
+            }
+            __syncwarp();
           }
         }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
+    // ===== MMA issuer: uniform control flow for the whole warp, the MMAs and commits under tc::elect_one() =====
+    {
       constexpr uint32_t idesc = tc::idesc_tf32(TC_BM, TC_BN), idesc2 = tc::idesc_tf32(TC_BM, 2 * TC_BN);
       (void)idesc2;
       uint32_t it = 0, tl = 0;
@@ -346,23 +356,26 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constan
           unsigned char *st = smem + s * STAGE_BYTES;
           if (RAW_A) {
             tc::mbar_wait(&full[s], ph);
-            tc_trace(p, 1, it, 0);
+            if (lane == 0) tc_trace(p, 1, it, 0);
             tc::mbar_wait(&tfull[s], ph);
-            tc_trace(p, 1, it, 1);
+            if (lane == 0) tc_trace(p, 1, it, 1);
             tc::tc_fence_after();
             const uint32_t t_hi = tmem + A_RING_COL + (uint32_t)s * 64u, t_lo = t_hi + 32u;
             const uint64_t d_bhi = tc::smem_desc_k_sw128(st + 1 * TC_TILE_BYTES);  // B_lo follows at + 16 KB
+            if (tc::elect_one()) {
 #pragma unroll
-            for (int k = 0; k < TC_BK / 8; ++k) {
-              const uint32_t off = (uint32_t)k * 32u, col = (uint32_t)k * 8u;  // 8 TF32 = 32 bytes = 8 TMEM columns
-              const uint32_t acc = (kb == 0 && k == 0) ? 0u : 1u;
-              // B_hi and B_lo are adjacent 128-row tiles: one N = 256 MMA writes [hi·hi | hi·lo] into [main | corr]
-              tc::mma_tf32_ts(acc_main, t_hi + col, tc::smem_desc_advance(d_bhi, off), idesc2, acc);
-              tc::mma_tf32_ts(acc_corr, t_lo + col, tc::smem_desc_advance(d_bhi, off), idesc, 1u);
+              for (int k = 0; k < TC_BK / 8; ++k) {
+                const uint32_t off = (uint32_t)k * 32u, col = (uint32_t)k * 8u;  // 8 TF32 = 32 bytes = 8 TMEM columns
+                const uint32_t acc = (kb == 0 && k == 0) ? 0u : 1u;
+                // B_hi and B_lo are adjacent 128-row tiles: one N = 256 MMA writes [hi·hi | hi·lo] into [main | corr]
+                tc::mma_tf32_ts(acc_main, t_hi + col, tc::smem_desc_advance(d_bhi, off), idesc2, acc);
+                tc::mma_tf32_ts(acc_corr, t_lo + col, tc::smem_desc_advance(d_bhi, off), idesc, 1u);
+              }
+              tc::mma_commit(&empty[s]);   // B stage free once these MMAs have read it
+              tc::mma_commit(&tempty[s]);  // and so is the TMEM stage of A
             }
-            tc::mma_commit(&empty[s]);   // B stage free once these MMAs have read it
-            tc::mma_commit(&tempty[s]);  // and so is the TMEM stage of A
-            tc_trace(p, 1, it, 2);
+            __syncwarp();
+            if (lane == 0) tc_trace(p, 1, it, 2);
           } else {
             tc::mbar_wait(&full[s], ph);
             tc::tc_fence_after();
@@ -370,18 +383,22 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap map_ahi, const __grid_constan
             const uint64_t d_alo = tc::smem_desc_k_sw128(st + 1 * TC_TILE_BYTES);
             const uint64_t d_bhi = tc::smem_desc_k_sw128(st + 2 * TC_TILE_BYTES);
             const uint64_t d_blo = tc::smem_desc_k_sw128(st + 3 * TC_TILE_BYTES);
+            if (tc::elect_one()) {
 #pragma unroll
-            for (int k = 0; k < TC_BK / 8; ++k) {
-              const uint32_t off = (uint32_t)k * 32u;  // 8 TF32 = 32 bytes inside the swizzled 128-byte row
-              const uint32_t acc = (kb == 0 && k == 0) ? 0u : 1u;
-              tc::mma_tf32(acc_main, tc::smem_desc_advance(d_ahi, off), tc::smem_desc_advance(d_bhi, off), idesc, acc);
-              tc::mma_tf32(acc_corr, tc::smem_desc_advance(d_ahi, off), tc::smem_desc_advance(d_blo, off), idesc, acc);
-              tc::mma_tf32(acc_corr, tc::smem_desc_advance(d_alo, off), tc::smem_desc_advance(d_bhi, off), idesc, 1u);
+              for (int k = 0; k < TC_BK / 8; ++k) {
+                const uint32_t off = (uint32_t)k * 32u;  // 8 TF32 = 32 bytes inside the swizzled 128-byte row
+                const uint32_t acc = (kb == 0 && k == 0) ? 0u : 1u;
+                tc::mma_tf32(acc_main, tc::smem_desc_advance(d_ahi, off), tc::smem_desc_advance(d_bhi, off), idesc, acc);
+                tc::mma_tf32(acc_corr, tc::smem_desc_advance(d_ahi, off), tc::smem_desc_advance(d_blo, off), idesc, acc);
+                tc::mma_tf32(acc_corr, tc::smem_desc_advance(d_alo, off), tc::smem_desc_advance(d_bhi, off), idesc, 1u);
+              }
+              tc::mma_commit(&empty[s]);  // frees the stage once these MMAs have read it
             }
-            tc::mma_commit(&empty[s]);  // frees the stage once these MMAs have read it
+            __syncwarp();
           }
         }
-        tc::mma_commit(&acc_full[a]);
+        if (tc::elect_one()) tc::mma_commit(&acc_full[a]);
+        __syncwarp();
         ++tl;
       }
     }
@@ -603,8 +620,8 @@ gemm_tc_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
   };
 
   if (warp == 0) {
-    // ===== TMA producer =====
-    if (lane == 0) {
+    // ===== TMA producer (whole warp, elected lane issues) =====
+    {
       uint32_t it = 0;
       for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
         int64_t z, mb, nb, k_begin;
@@ -612,30 +629,37 @@ gemm_tc_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
         tile_coords(tile, z, mb, nb, nkb, k_begin);
         const int32_t m0 = (int32_t)(mb * TC_BM);
         int32_t n0 = (int32_t)(nb * TC_BN);
-        const CUtensorMap *mapb = &map_b1;
-        if (n0 >= p.k_a2) {  // k_a2 = width of the first B source (a multiple of TC_BN)
-          mapb = &map_b2;
-          n0 -= (int32_t)p.k_a2;
-        }
+        const bool second = n0 >= p.k_a2;  // k_a2 = width of the first B source (a multiple of TC_BN)
+        if (second) n0 -= (int32_t)p.k_a2;
         for (int kb = 0; kb < nkb; ++kb, ++it) {
           const int s = it % STAGES;
           const uint32_t ph = (it / STAGES) & 1u;
           unsigned char *st = smem + s * STAGE_BYTES;
           const int32_t kc = (int32_t)(k_begin + (int64_t)kb * TC_BK);
           tc::mbar_wait(&aempty[s], ph ^ 1u);
-          tc::mbar_expect_tx(&afull[s], TC_TILE_BYTES);
-          tc::tma_load_2d(st, &map_a, &afull[s], m0, kc);
+          if (tc::elect_one()) {
+            tc::mbar_expect_tx(&afull[s], TC_TILE_BYTES);
+            tc::tma_load_2d(st, &map_a, &afull[s], m0, kc);
+          }
+          __syncwarp();
           tc::mbar_wait(&empty[s], ph ^ 1u);
-          tc::mbar_expect_tx(&full[s], TC_TILE_BYTES);
+          if (tc::elect_one()) {
+            tc::mbar_expect_tx(&full[s], TC_TILE_BYTES);
 #pragma unroll
-          for (int j = 0; j < 4; ++j)
-            tc::tma_load_2d(st + TC_TILE_BYTES + j * 4096, mapb, &full[s], n0 + 32 * j, kc);
+            for (int j = 0; j < 4; ++j) {
+              if (second)
+                tc::tma_load_2d(st + TC_TILE_BYTES + j * 4096, &map_b2, &full[s], n0 + 32 * j, kc);
+              else
+                tc::tma_load_2d(st + TC_TILE_BYTES + j * 4096, &map_b1, &full[s], n0 + 32 * j, kc);
+            }
+          }
+          __syncwarp();
         }
       }
     }
   } else if (warp == 1) {
-    // ===== MMA issuer =====
-    if (lane == 0) {
+    // ===== MMA issuer (whole warp, elected lane issues) =====
+    {
       constexpr uint32_t idesc = tc::idesc_tf32_bmn(TC_BM, TC_BN), idesc2 = tc::idesc_tf32_bmn(TC_BM, 2 * TC_BN);
       uint32_t it = 0, tl = 0;
       for (int64_t tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
@@ -654,17 +678,21 @@ gemm_tc_tn_kernel(const __grid_constant__ CUtensorMap map_a, const __grid_consta
           tc::tc_fence_after();
           const uint32_t t_hi = tmem + A_RING_COL + (uint32_t)s * 64u, t_lo = t_hi + 32u;
           const uint64_t d_bhi = tc::smem_desc_mn_sw128_32b(st + TC_TILE_BYTES);  // B_lo = the next four 4 KB blocks
+          if (tc::elect_one()) {
 #pragma unroll
-          for (int k = 0; k < TC_BK / 8; ++k) {
-            const uint32_t off = (uint32_t)k * 1024u, col = (uint32_t)k * 8u;  // 8 K-rows of 128 bytes
-            const uint32_t acc = (kb == 0 && k == 0) ? 0u : 1u;
-            tc::mma_tf32_ts(acc_main, t_hi + col, tc::smem_desc_advance(d_bhi, off), idesc2, acc);
-            tc::mma_tf32_ts(acc_corr, t_lo + col, tc::smem_desc_advance(d_bhi, off), idesc, 1u);
+            for (int k = 0; k < TC_BK / 8; ++k) {
+              const uint32_t off = (uint32_t)k * 1024u, col = (uint32_t)k * 8u;  // 8 K-rows of 128 bytes
+              const uint32_t acc = (kb == 0 && k == 0) ? 0u : 1u;
+              tc::mma_tf32_ts(acc_main, t_hi + col, tc::smem_desc_advance(d_bhi, off), idesc2, acc);
+              tc::mma_tf32_ts(acc_corr, t_lo + col, tc::smem_desc_advance(d_bhi, off), idesc, 1u);
+            }
+            tc::mma_commit(&empty[s]);
+            tc::mma_commit(&tempty[s]);
           }
-          tc::mma_commit(&empty[s]);
-          tc::mma_commit(&tempty[s]);
+          __syncwarp();
         }
-        tc::mma_commit(acc_full);
+        if (tc::elect_one()) tc::mma_commit(acc_full);
+        __syncwarp();
         ++tl;
       }
     }
@@ -810,7 +838,7 @@ static EncodeTiledFn encode_tiled_fn() {
 
 // [rows, k] fp32 row-major (leading dimension ld elements) -> boxes of 128 rows x 32 columns, 128B swizzle,
 // out-of-range elements read as zero (ragged M, N and K tails need no masking in the kernel)
-static int make_operand_map(CUtensorMap *map, const float *base, int64_t rows, int64_t k, int64_t ld) {
+int tc_make_operand_map(CUtensorMap *map, const float *base, int64_t rows, int64_t k, int64_t ld) {
   EncodeTiledFn enc = encode_tiled_fn();
   if (!enc) {
     set_error("gemm_tc: cuTensorMapEncodeTiled is not available from this driver");
@@ -900,14 +928,14 @@ static int launch_gemm_tc(const float *ahi, const float *alo, const float *bhi, 
       set_error("gemm_tc: the second raw A source needs k_a2 %% %d == 0 and lda2 %% 4 == 0", TC_BK);
       return GDR_E_SHAPE;
     }
-    if ((rc = make_operand_map(&ma, ahi, m, k_a2, lda))) return rc;
-    if ((rc = make_operand_map(&ml, k_a2 < k ? alo : ahi, m, k_a2 < k ? k - k_a2 : k_a2, k_a2 < k ? lda2 : lda))) return rc;
+    if ((rc = tc_make_operand_map(&ma, ahi, m, k_a2, lda))) return rc;
+    if ((rc = tc_make_operand_map(&ml, k_a2 < k ? alo : ahi, m, k_a2 < k ? k - k_a2 : k_a2, k_a2 < k ? lda2 : lda))) return rc;
   } else {
-    if ((rc = make_operand_map(&ma, ahi, m, k, lda))) return rc;
-    if ((rc = make_operand_map(&ml, alo, m, k, lda))) return rc;
+    if ((rc = tc_make_operand_map(&ma, ahi, m, k, lda))) return rc;
+    if ((rc = tc_make_operand_map(&ml, alo, m, k, lda))) return rc;
   }
-  if ((rc = make_operand_map(&mb, bhi, n, k, ldb))) return rc;
-  if ((rc = make_operand_map(&mbl, blo, n, k, ldb))) return rc;
+  if ((rc = tc_make_operand_map(&mb, bhi, n, k, ldb))) return rc;
+  if ((rc = tc_make_operand_map(&mbl, blo, n, k, ldb))) return rc;
   TcParams p{};
   p.m = m; p.n = n; p.k = k; p.k_per_split = k_per_split; p.splits = splits > 0 ? splits : 1;
   p.k_a2 = RAW_A ? k_a2 : k; p.g = g; p.trace = g_tc_trace;

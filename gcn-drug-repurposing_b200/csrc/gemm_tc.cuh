@@ -1,5 +1,7 @@
 // gemm_tc.cuh — host entry points of the tcgen05 3xTF32 GEMM (gemm_tc.cu) for the other translation units.
 #pragma once
+#include <cuda.h>  // CUtensorMap
+
 #include "gemm_simt.cuh"
 
 namespace gdr {
@@ -28,6 +30,13 @@ int tc_gemm_raw_a(int epi, const float *a1, int64_t lda1, int64_t k1, const floa
 int tc_gemm_tn_splitk(const float *a, int64_t lda, int64_t m, const float *b1, int64_t ldb1, int64_t n1,
                       const float *b2, int64_t ldb2, int64_t n2, int64_t k, int64_t k_per_split, int splits,
                       float *part, float *colsum_part, cudaStream_t st);
+
+// TMA map of a K-major fp32 operand [rows, k] (leading dimension ld): boxes of 128 rows x 32 columns, SWIZZLE_128B,
+// out-of-range elements read as zero
+int tc_make_operand_map(CUtensorMap *map, const float *base, int64_t rows, int64_t k, int64_t ld);
+
+// the buffer set by gdr_debug_tc_trace (nullptr: tracing off)
+long long *tc_trace_buffer();
 
 constexpr int TC_K_ALIGN = 32;  // split-K ranges must be multiples of the 32-column TMA box
 

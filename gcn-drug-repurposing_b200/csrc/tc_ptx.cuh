@@ -37,6 +37,21 @@ __device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity) {
       : "memory");
 }
 
+// one lane of a fully converged warp (elect.sync): the form ptxas recognises as "exactly one thread is active", so the
+// uniform-datapath operands of tcgen05.mma / commit need no per-instruction ELECT + R2UR.BROADCAST waterfall loop
+// (which `if (lane == 0)` produces: ~80 clk per MMA issue, measured)
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile(
+      "{\n\t"
+      ".reg .pred p;\n\t"
+      "elect.sync _|p, 0xffffffff;\n\t"
+      "selp.u32 %0, 1, 0, p;\n\t"
+      "}"
+      : "=r"(pred));
+  return pred != 0u;
+}
+
 // ---- TMA: 2-D tile, global -> shared, completion counted on an mbarrier ------------------------
 __device__ __forceinline__ void tma_load_2d(void *smem_dst, const CUtensorMap *map, uint64_t *bar, int32_t c0,
                                             int32_t c1) {

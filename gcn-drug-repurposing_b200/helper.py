@@ -26,15 +26,39 @@ def _device():
     return torch.device("cuda", torch.cuda.current_device())
 
 
-def gram_topk(x_rows, k):
+GRAM_TOPK_TC_MAX_D = 256   # operand A of the tensor-core kernel lives in tensor memory (256 + d <= 512 columns)
+GRAM_TOPK_TC_MAX_K = 16
+last_gram_topk_info = {}   # backend and number of rows that took the exact fp64 path in the last gram_topk call
+
+
+def gram_topk(x_rows, k, backend=None):
     """x_rows: [n, d] fp64 CUDA tensor.  Returns (idx int32 [n,k], val fp64 [n,k]) of the k largest
-    entries of every row of x_rows·x_rowsᵀ, by descending value."""
+    entries of every row of x_rows·x_rowsᵀ (helpers/helper.py:39,44), by descending value.
+
+    backend "tc" (default when d <= 256 and k <= 16, GDR_GEMM != simt): TF32 Gram tiles on tcgen05 with the
+    top-k fused into the epilogue, exact fp64 re-rank of the candidates, certified per row, uncertified rows
+    recomputed in fp64 (gdr_gram_topk_tc_f64).  backend "f64": the fp64 SIMT kernel (gdr_gram_topk_f64).
+    Both give the same index sets and values, fp64 ties excepted."""
     L = _ffi.lib()
     n, d = x_rows.shape
+    if backend is None:
+        from . import model as _model
+        backend = "tc" if (_model.GEMM_BACKEND == "tc" and d <= GRAM_TOPK_TC_MAX_D and k <= GRAM_TOPK_TC_MAX_K) else "f64"
     idx = torch.empty(n, k, dtype=torch.int32, device=x_rows.device)
     val = torch.empty(n, k, dtype=torch.float64, device=x_rows.device)
-    _ffi.check(L.gdr_gram_topk_f64(_ffi.ptr(x_rows), n, d, k, _ffi.ptr(idx), _ffi.ptr(val), _ffi.stream()),
-               "gram_topk_f64")
+    last_gram_topk_info.clear()
+    last_gram_topk_info["backend"] = backend
+    if backend == "tc":
+        ws = _ffi.workspace(L.gdr_gram_topk_tc_workspace_bytes(n, d, k), x_rows.device)
+        nfb = torch.zeros(1, dtype=torch.int32, device=x_rows.device)
+        _ffi.check(L.gdr_gram_topk_tc_f64(_ffi.ptr(x_rows), n, d, k, _ffi.ptr(idx), _ffi.ptr(val), _ffi.ptr(nfb),
+                                          _ffi.ptr(ws), ws.numel(), _ffi.stream()), "gram_topk_tc_f64")
+        last_gram_topk_info["fallback_rows"] = nfb   # device tensor: reading it synchronises, so leave that to the caller
+    elif backend == "f64":
+        _ffi.check(L.gdr_gram_topk_f64(_ffi.ptr(x_rows), n, d, k, _ffi.ptr(idx), _ffi.ptr(val), _ffi.stream()),
+                   "gram_topk_f64")
+    else:
+        raise ValueError(f"gram_topk: unknown backend {backend!r}")
     return idx, val
 
 
@@ -118,13 +142,8 @@ def gen_graph(Q, X, kq=5, k=5, q_RANSAC_graph=None, x_RANSAC_graph=None):
 
     # --- index graph ------------------------------------------------------------------------------
     if x_RANSAC_graph is not None:
-        top = np.asarray(x_RANSAC_graph)[:, 0:k].astype(np.int64)
-        rows = np.repeat(np.arange(n), top.shape[1])
-        cols = top.reshape(-1)
-        vals = np.einsum("ij,ij->j", X[:, rows], X[:, cols])
-        keep = rows != cols
-        a = sp.coo_matrix((vals[keep], (rows[keep], cols[keep])), shape=(n, n)).tocsr()
-        a.data[:] = 1.0  # structure only; values re-read below
+        # helpers/helper.py:41-42 takes the first k columns of a precomputed retrieval graph; those .npy files belong
+        # to the image-retrieval datasets the reference was forked from and are absent upstream too
         raise NotImplementedError("ransac graph modes need the retrieval datasets (absent upstream too)")
     x_adj = knn_adjacency(x_rows, k)
 

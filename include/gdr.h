@@ -235,6 +235,17 @@ int gdr_gram_percentile_f32(const float *h, int64_t n, int64_t d, double q_perce
  * [n,k] sorted by descending similarity, values fp64 [n,k].  N×N is never stored.     */
 int gdr_gram_topk_f64(const double *x, int64_t n, int64_t d, int64_t k,
                       int32_t *idx_out, double *val_out, gdr_stream_t stream);
+/* The same result with the N×N contraction on the tcgen05 tensor cores and the selection fused into its
+ * epilogue (gram_topk_tc.cu): TF32 Gram tiles (operand A resident in tensor memory, B streamed by TMA) keep
+ * the C largest approximate similarities per row and column range, the candidates are re-ranked with exact
+ * fp64 inner products, and a row whose k-th exact value is not provably above everything that was dropped
+ * (margin 1.1e-3·|x_i|·max|x_j|) is recomputed by the exact fp64 kernel — so idx_out/val_out equal
+ * gdr_gram_topk_f64's (order: value descending, then column ascending), fp64 ties excepted.  d <= 256,
+ * k <= 16.  n_fallback_out (device int32, may be NULL) receives the number of rows that took the fp64 path. */
+int64_t gdr_gram_topk_tc_workspace_bytes(int64_t n, int64_t d, int64_t k);
+int gdr_gram_topk_tc_f64(const double *x, int64_t n, int64_t d, int64_t k, int32_t *idx_out,
+                         double *val_out, int32_t *n_fallback_out, void *workspace,
+                         int64_t workspace_bytes, gdr_stream_t stream);
 
 /* ---- optimizer ------------------------------------------------------------------------ *
  * torch.optim.Adam single step (train.py:139,184), one launch for all tensors laid out
