@@ -75,6 +75,12 @@ _SIGNATURES = {
     "gdr_gram_topk_f64": (c_i32, [c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr]),
     "gdr_gram_topk_tc_workspace_bytes": (c_i64, [c_i64, c_i64, c_i64]),
     "gdr_gram_topk_tc_f64": (c_i32, [c_ptr, c_i64, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_i64, c_ptr]),
+    "gdr_bias_act_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i64, c_i32, c_ptr, c_ptr]),
+    "gdr_act_bwd_colsum_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i64, c_i32, c_ptr, c_ptr, c_ptr]),
+    "gdr_dropout_apply_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_f32, c_ptr, c_ptr, c_ptr]),
+    "gdr_masked_softmax_ce_workspace_bytes": (c_i64, [c_i64]),
+    "gdr_masked_softmax_ce_f32": (c_i32, [c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_i64,
+                                          c_ptr]),
     "gdr_text_savetxt_bytes": (c_i64, [c_i64, c_i64]),
     "gdr_text_savetxt_e18": (c_i64, [c_ptr, c_i64, c_i64, c_i32, ctypes.c_char_p, c_i64, c_i32]),
     "gdr_text_parse_embs": (c_i64, [ctypes.c_char_p, c_i64, c_i32, c_ptr, c_i64, c_ptr, c_ptr,

@@ -999,6 +999,19 @@ int tc_gemm_raw_a(int epi, const float *a1, int64_t lda1, int64_t k1, const floa
   return GDR_E_BADARG;
 }
 
+// split-K form of the above for products with few output tiles and a long reduction (dE[panel] = 2dG[panel, :]·E with
+// K = B): part[z][m][n] = A[:, K range z] · B[:, K range z]ᵀ, reduced by the caller in a fixed order
+int tc_gemm_raw_a_splitk(const float *a, int64_t lda, int64_t k, const float *bhi, const float *blo, int64_t ldb,
+                         int64_t m, int64_t n, int64_t k_per_split, int splits, float *part, cudaStream_t st) {
+  if (k_per_split % TC_BK) {
+    set_error("gemm_tc: split-K ranges must be multiples of %d", TC_BK);
+    return GDR_E_SHAPE;
+  }
+  GemmParams g{};
+  g.c = part; g.ldc = n;
+  return launch_gemm_tc<EPI_SPLITK, true>(a, nullptr, bhi, blo, m, n, k, lda, ldb, k_per_split, splits, g, st, k, 0);
+}
+
 }  // namespace gdr
 
 using namespace gdr;

@@ -24,6 +24,10 @@ int tc_gemm_raw_a(int epi, const float *a1, int64_t lda1, int64_t k1, const floa
                   const float *bhi, const float *blo, int64_t ldb, int64_t m, int64_t n, const GemmParams &g,
                   cudaStream_t st);
 
+// raw-A product cut along K: part[z][m][n] over K ranges of k_per_split columns (multiple of 32); n % 4 == 0
+int tc_gemm_raw_a_splitk(const float *a, int64_t lda, int64_t k, const float *bhi, const float *blo, int64_t ldb,
+                         int64_t m, int64_t n, int64_t k_per_split, int splits, float *part, cudaStream_t st);
+
 // TN form on raw operands: part[z][m][n1 + n2] = A[K range z, 0:m]ᵀ · [B1 | B2][K range z, :], A [k, m] and B1/B2
 // [k, n1] / [k, n2] row-major (n1, n2 multiples of 128; n2 == 0: one source), K ranges of k_per_split rows
 // (a multiple of 32).  colsum_part[z][m] (optional) receives the column sums of A over each K range.

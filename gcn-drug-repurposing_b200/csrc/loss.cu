@@ -6,6 +6,10 @@
 //
 // Forward and gradient come out of one call: the Gram GEMM's epilogue turns each G tile
 // into (loss partial, 2·dG tile) in registers, a second GEMM contracts 2·dG with E.
+#include <stdlib.h>
+
+#include <algorithm>
+
 #include "gemm_tc.cuh"
 
 namespace gdr {
@@ -197,12 +201,73 @@ int gdr_adam_step_f32(float *param, const float *grad, float *exp_avg, float *ex
 }
 
 // ---- tcgen05 variant: Gram and dG·E on the tensor cores (3xTF32, csrc/gemm_tc.cu) -------------------------
+// The B x B matrices are never stored: the rows are processed in PANELS of R rows (R * B * 4 bytes <= 1 GiB).  Per
+// panel one Gram GEMM (epilogue: loss partials + the 2·dG panel) and one product dE[panel] = (2·dG panel)·E; the loss
+// partials of a panel are folded into one fp64 accumulator in a fixed order.  `index == NULL` with B = N = 2^20
+// (train.py --batch-size 0, SURVEY 8 a9: "10^12 entries, must be tiled, never stored") needs 4 GB of panel instead of
+// 4 TB; a B that fits one panel (every minibatch) takes exactly the two GEMMs it always did.
+constexpr int64_t GSS_PANEL_BYTES = (int64_t)1 << 30;
+
+static int64_t gss_panel_rows(int64_t b) {
+  const int64_t ldw = align_up(b > 0 ? b : 1, 4);
+  int64_t r = GSS_PANEL_BYTES / (ldw * 4);
+  if (const char *env = getenv("GDR_GSS_PANEL_ROWS")) r = atoll(env);  // tests: force several panels at small B
+  r = r / 128 * 128;
+  if (r < 128) r = 128;
+  return r < b ? r : b;
+}
+
+// dE panel = 2dG panel · E has few output tiles (rows/128 x d/128) and K = B: cut K so that every SM has a tile
+static void gss_splitk_plan(int64_t rows, int64_t d, int64_t k, int &splits, int64_t &k_per_split) {
+  const int64_t tiles = ceil_div<int64_t>(rows, 128) * ceil_div<int64_t>(d, 128);
+  int64_t want = ceil_div<int64_t>(kNumSMs, tiles);
+  const int64_t kblocks = ceil_div<int64_t>(k, 32);
+  want = std::max<int64_t>(1, std::min<int64_t>(want, ceil_div<int64_t>(kblocks, 16)));  // >= 16 k-blocks per range
+  k_per_split = ceil_div<int64_t>(kblocks, want) * 32;
+  splits = (int)ceil_div<int64_t>(k, k_per_split);
+}
+
+// upper bound of splits * r * d for every panel height r <= rows: splits <= 148 / tiles + 1 and r * d <= tiles * 128^2
+static int64_t gss_part_floats(int64_t rows, int64_t d) {
+  const int64_t tiles = ceil_div<int64_t>(rows > 0 ? rows : 1, 128) * ceil_div<int64_t>(d, 128);
+  return (kNumSMs + tiles) * 128 * 128;
+}
+
+// out[i] = sum_z part[z][i], z ascending (deterministic)
+__global__ void __launch_bounds__(256)
+gss_splitk_reduce_kernel(const float *__restrict__ part, int splits, int64_t count, float *__restrict__ out) {
+  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+  if (i >= count) return;
+  float4 s = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int z = 0; z < splits; ++z) {
+    const float4 v = ldg_f4(part + (int64_t)z * count + i);
+    s.x += v.x; s.y += v.y; s.z += v.z; s.w += v.w;
+  }
+  *reinterpret_cast<float4 *>(out + i) = s;
+}
+
+__global__ void loss_accumulate_kernel(const double *__restrict__ partials, int64_t count, double *__restrict__ acc,
+                                       int first) {
+  __shared__ double red[32];
+  double s = 0.0;
+  for (int64_t i = threadIdx.x; i < count; i += blockDim.x) s += partials[i];
+  s = warp_sum(s);
+  if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = s;
+  __syncthreads();
+  if (threadIdx.x == 0) {
+    double tot = 0.0;
+    for (int w = 0; w < (int)(blockDim.x >> 5); ++w) tot += red[w];
+    *acc = first ? tot : *acc + tot;
+  }
+}
+
 int64_t gdr_gss_loss_tc_workspace_bytes(int64_t b, int64_t d) {
   if (b < 0 || d <= 0) return GDR_E_BADARG;
   const int64_t ldw = align_up(b, 4);
-  const int64_t tiles = ceil_div<int64_t>(b > 0 ? b : 1, 128);
-  return 3 * align_up(b * d * 4, 256) + 3 * align_up(b * ldw * 4, 256) + 2 * align_up(d * ldw * 4, 256) +
-         align_up(tiles * tiles * 8, 256) + 2048;
+  const int64_t r = gss_panel_rows(b);
+  const int64_t tiles_b = ceil_div<int64_t>(b > 0 ? b : 1, 128), tiles_r = ceil_div<int64_t>(r > 0 ? r : 1, 128);
+  return 3 * align_up(b * d * 4, 256) + align_up(r * ldw * 4, 256) + 2 * align_up(d * ldw * 4, 256) +
+         align_up(tiles_r * tiles_b * 8, 256) + align_up(gss_part_floats(r, d) * 4, 256) + 2048;
 }
 
 int gdr_gss_loss_fwd_bwd_tc_f32(const float *embs, const int64_t *index, int64_t b, int64_t n, int64_t d, float alpha,
@@ -212,32 +277,58 @@ int gdr_gss_loss_fwd_bwd_tc_f32(const float *embs, const int64_t *index, int64_t
   GDR_CHECK_ARG(d % 4 == 0, GDR_E_SHAPE, "gss_loss_tc: d must be a multiple of 4");
   GDR_CHECK_ARG(embs && loss_out && grad_e_out && workspace, GDR_E_BADARG, "gss_loss_tc: null pointer");
   GDR_CHECK_ARG(workspace_bytes >= gdr_gss_loss_tc_workspace_bytes(b, d), GDR_E_WORKSPACE,
-                "gss_loss_tc: workspace too small (B=%lld needs BxB tile buffers)", (long long)b);
+                "gss_loss_tc: workspace too small");
   cudaStream_t st = as_stream(stream);
   const int64_t ldw = align_up(b, 4);
-  const int64_t tiles = ceil_div<int64_t>(b, 128);
+  const int64_t rows = gss_panel_rows(b);
+  const int64_t tiles_b = ceil_div<int64_t>(b, 128);
   Carver cv(workspace);
   float *e = cv.take<float>(b * d), *ehi = cv.take<float>(b * d), *elo = cv.take<float>(b * d);
-  float *wm = cv.take<float>(b * ldw), *whi = cv.take<float>(b * ldw), *wlo = cv.take<float>(b * ldw);
+  float *wm = cv.take<float>(rows * ldw);
   float *ethi = cv.take<float>(d * ldw), *etlo = cv.take<float>(d * ldw);
-  double *partials = cv.take<double>(tiles * tiles);
-  gather_rows_kernel<<<(unsigned)ceil_div<int64_t>(b * 32, 256), 256, 0, st>>>(embs, index, b, n, d, e);
-  GDR_LAUNCHED();
+  double *partials = cv.take<double>(ceil_div<int64_t>(rows, 128) * tiles_b);
+  double *acc = cv.take<double>(1);
+  float *part = cv.take<float>(gss_part_floats(rows, d));
+  const float *esrc = embs;  // index == NULL: E is embs itself, no copy
+  if (index != nullptr) {
+    gather_rows_kernel<<<(unsigned)ceil_div<int64_t>(b * 32, 256), 256, 0, st>>>(embs, index, b, n, d, e);
+    GDR_LAUNCHED();
+    esrc = e;
+  }
   int rc;
-  if ((rc = tc_split(e, d, d, nullptr, 0, 0, b, ehi, elo, st))) return rc;
-  if ((rc = tc_split_transpose(e, d, b, d, ldw, ethi, etlo, st))) return rc;  // Eᵀ [d, ldw], zero padded
-  GemmParams g{};
-  g.c = wm; g.ldc = ldw;
-  g.alpha = alpha; g.beta = beta;
-  g.wscale = (float)(2.0 / ((double)b * (double)b));
-  g.loss_partials = partials;
-  if ((rc = tc_gemm(EPI_GSS, ehi, elo, ehi, elo, b, b, d, d, d, d, 1, g, st))) return rc;   // G = E·Eᵀ -> loss, 2·dG
-  loss_finalize_kernel<<<1, 256, 0, st>>>(partials, (int)(tiles * tiles), 1.0 / ((double)b * (double)b), loss_out);
+  if ((rc = tc_split(esrc, d, d, nullptr, 0, 0, b, ehi, elo, st))) return rc;
+  if ((rc = tc_split_transpose(esrc, d, b, d, ldw, ethi, etlo, st))) return rc;  // Eᵀ [d, ldw], zero padded
+  for (int64_t r0 = 0; r0 < b; r0 += rows) {
+    const int64_t r = std::min<int64_t>(rows, b - r0);
+    const int64_t tiles_r = ceil_div<int64_t>(r, 128);
+    GemmParams g{};
+    g.c = wm; g.ldc = ldw;
+    g.alpha = alpha; g.beta = beta;
+    g.wscale = (float)(2.0 / ((double)b * (double)b));
+    g.loss_partials = partials;
+    // G panel = E[r0:r0+r]·Eᵀ -> loss partials, 2·dG panel
+    if ((rc = tc_gemm(EPI_GSS, ehi + r0 * d, elo + r0 * d, ehi, elo, r, b, d, d, d, d, 1, g, st))) return rc;
+    loss_accumulate_kernel<<<1, 1024, 0, st>>>(partials, tiles_r * tiles_b, acc, r0 == 0 ? 1 : 0);
+    GDR_LAUNCHED();
+    // dE[panel] = 2·dG panel · E   (the panel is split into TF32 hi/lo inside the kernel; K = B is cut into ranges so
+    // that the few output tiles of a panel still occupy every SM, partials reduced in range order)
+    int splits;
+    int64_t kps;
+    gss_splitk_plan(r, d, ldw, splits, kps);
+    if (splits == 1) {
+      GemmParams q{};
+      q.c = grad_e_out + r0 * d; q.ldc = d;
+      if ((rc = tc_gemm_raw_a(EPI_STORE, wm, ldw, ldw, nullptr, 0, 0, ethi, etlo, ldw, r, d, q, st))) return rc;
+    } else {
+      if ((rc = tc_gemm_raw_a_splitk(wm, ldw, ldw, ethi, etlo, ldw, r, d, kps, splits, part, st))) return rc;
+      gss_splitk_reduce_kernel<<<(unsigned)ceil_div<int64_t>(r * d / 4, 256), 256, 0, st>>>(part, splits, r * d,
+                                                                                         grad_e_out + r0 * d);
+      GDR_LAUNCHED();
+    }
+  }
+  loss_finalize_kernel<<<1, 32, 0, st>>>(acc, 1, 1.0 / ((double)b * (double)b), loss_out);
   GDR_LAUNCHED();
-  (void)whi; (void)wlo;                                                                     // 2·dG is split in-kernel
-  GemmParams q{};
-  q.c = grad_e_out; q.ldc = d;
-  return tc_gemm_raw_a(EPI_STORE, wm, ldw, ldw, nullptr, 0, 0, ethi, etlo, ldw, b, d, q, st);  // dE = 2·dG · E
+  return GDR_OK;
 }
 
 int gdr_adam_step_multi_f32(int n_tensors, float *const *params, const float *const *grads, float *const *exp_avg,

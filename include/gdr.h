@@ -247,6 +247,27 @@ int gdr_gram_topk_tc_f64(const double *x, int64_t n, int64_t d, int64_t k, int32
                          double *val_out, int32_t *n_fallback_out, void *workspace,
                          int64_t workspace_bytes, gdr_stream_t stream);
 
+/* ---- Kipf & Welling graph convolution (multiscale/openne/gcn/layers.py:133-190, metrics.py:4-21) ----------- *
+ * act(sum_i A_i·(X·W_i) + b): the products are gdr_spmm_csr_f32 (supports, sparse X) and gdr_gemm_nt_tc_f32
+ * (dense X·W, dW, dX); these are the row-local pieces.                                                     */
+/* y = act(z + bias)   (bias may be NULL; relu != 0: ReLU, else identity; y may alias z) */
+int gdr_bias_act_f32(const float *z, const float *bias, int64_t n, int64_t d, int relu, float *y,
+                     gdr_stream_t stream);
+/* dz = dy ⊙ [y > 0] (relu != 0) or dy; db = column sums of dz.  dz and db may be NULL (not wanted). */
+int gdr_act_bwd_colsum_f32(const float *dy, const float *y, int64_t n, int64_t d, int relu, float *dz,
+                           float *db, gdr_stream_t stream);
+/* y = x * floor(keep_prob + u) / keep_prob  (layers.py:22-29, tf.nn.dropout); u: uniform [0,1) numbers from the
+ * caller's generator; mask_scale_out (may be NULL) keeps the factor for the backward pass.                */
+int gdr_dropout_apply_f32(const float *x, const float *uniform, int64_t count, float keep_prob, float *y,
+                          float *mask_scale_out, gdr_stream_t stream);
+/* masked_softmax_cross_entropy + masked_accuracy (metrics.py:4-21) and dLoss/dLogits in one pass.
+ * logits [n, ld] (ld >= c: padded rows allowed), labels [n, c], mask [n] (0/1 as fp32).                   */
+int64_t gdr_masked_softmax_ce_workspace_bytes(int64_t n);
+int gdr_masked_softmax_ce_f32(const float *logits, int64_t ld, const float *labels, const float *mask,
+                              int64_t n, int64_t c, float *loss_out, float *accuracy_out,
+                              float *dlogits_out, void *workspace, int64_t workspace_bytes,
+                              gdr_stream_t stream);
+
 /* ---- optimizer ------------------------------------------------------------------------ *
  * torch.optim.Adam single step (train.py:139,184), one launch for all tensors laid out
  * back to back in flat buffers of `count` floats; step_dev: device int32 counter that

@@ -183,6 +183,41 @@ def test_gss_loss_tc_matches_simt(gdr, monkeypatch):
     assert_close(out["tc"][1], e.grad.numpy(), what="dLoss/dE tc vs torch cpu")
 
 
+@pytest.mark.parametrize("n,d,rows", [(1000, 128, 256), (1333, 64, 128), (600, 256, 384)])
+def test_gss_loss_full_batch_in_row_panels(gdr, monkeypatch, n, d, rows):
+    """index=None (train.py --batch-size 0): the B x B Gram is processed in row panels and never stored
+    (csrc/loss.cu).  Several panels (forced small) must give the loss and gradient of modules/model.py:214-221."""
+    g = torch.Generator(device=DEV).manual_seed(n)
+    h = torch.nn.functional.normalize(torch.randn(n, d, device=DEV, generator=g), dim=1)
+    res = {}
+    for name, env in (("one_panel", None), ("panels", str(rows))):
+        if env is None:
+            monkeypatch.delenv("GDR_GSS_PANEL_ROWS", raising=False)
+        else:
+            monkeypatch.setenv("GDR_GSS_PANEL_ROWS", env)
+        e = h.clone().requires_grad_(True)
+        loss = gdr.GSS_loss(1.0).gss_loss(embs=e, beta=0.15)
+        loss.backward()
+        torch.cuda.synchronize()
+        res[name] = (loss.item(), e.grad.cpu().numpy())
+    e = h.cpu().double().clone().requires_grad_(True)
+    ref = torch.mean(-0.5 * (torch.relu(torch.mm(e, e.t())) - 0.15) ** 2)
+    ref.backward()
+    for name in res:
+        assert_close(res[name][0], ref.item(), what=f"loss ({name}) vs torch fp64")
+        assert_close(res[name][1], e.grad.numpy(), what=f"dLoss/dE ({name}) vs torch fp64")
+    assert_close(res["panels"][1], res["one_panel"][1], what="panels vs one panel")
+
+
+def test_gss_loss_full_batch_workspace_is_bounded(gdr):
+    """B = 2^20, d = 256 (RMAT-20): the workspace is a few GB of panels, not the 4 TB of B x B."""
+    L = gdr._ffi.lib()
+    b, d = 1 << 20, 256
+    ws = L.gdr_gss_loss_tc_workspace_bytes(b, d)
+    assert ws < 12 * (1 << 30), ws
+    assert ws < b * b * 4 // 100
+
+
 @pytest.mark.parametrize("n,d,q", [(257, 128, 98.0), (600, 128, 98.0), (300, 256, 50.0), (130, 12, 0.0), (130, 12, 100.0)])
 def test_gram_percentile_tc(gdr, monkeypatch, n, d, q):
     from . import test_gpu_gcn
