@@ -46,6 +46,8 @@ L2_FLUSH_BYTES = 256 << 20
 DIST_ROW_WEIGHT = 6.0
 DIST_HUB_FIRST = 0
 DIST_SPLIT_PULL = 0
+DIST_FUSED_PUSH = 1          # the push product stores its partial rows straight into peer memory
+DIST_REBALANCE = 2           # rounds of measured-finish-time rebalancing of the L-shape bounds at set-up
 # L2 -> SM peak: ~6,300 bytes per clock for the whole chip (B300_MICROARCH.md, "LTS throughput cap", measured on
 # B300; no L2 figure in MEASURED_PEAKS.json), times the SM clock sampled during the run
 L2_BYTES_PER_CLK = 6300.0
@@ -74,6 +76,11 @@ def parse_args():
                         "per-source arrival signals instead of one barrier")
     p.add_argument("--no-rwr", action="store_true", help="skip the diffusion-profile measurement (configs[2]) at N=1")
     p.add_argument("--no-rmat20", action="store_true", help="skip the R-MAT-20 GCN measurement (configs[3]) at N=1")
+    p.add_argument("--fused-push", type=int, default=DIST_FUSED_PUSH,
+                   help="N>1, p2p: the push product stores its rows straight into the destination's receive region")
+    p.add_argument("--rebalance", type=int, default=DIST_REBALANCE,
+                   help="N>1, lshape: rounds of bounds refinement from the measured per-rank finish times (set-up)")
+    p.add_argument("--transposed", type=int, default=1, help="N>1: also measure A_hat^T G (second partition)")
     p.add_argument("--refine", action="store_true",
                    help="N>1, lshape: descend on the step timeline model from the cost-cap bounds (measured: no gain "
                         "at p = 8 on R-MAT 24, 7.5 vs 7.3 ms, so it is off by default)")
@@ -505,70 +512,162 @@ def run_rmat_spmm_dist(args):
     dist.init_process_group("nccl", device_id=dev, pg_options=opts, timeout=datetime.timedelta(seconds=180))
     full = build_rmat_csr(args.rmat_scale, args.rmat_edge_factor, dev)        # same seed on every rank
     n, d, nnz_total = full.n_rows, args.rmat_d, full.nnz
-    if args.partition == "lshape":
-        deg = (full.rowptr[1:] - full.rowptr[:-1]).to(torch.int64)
-        row_of = torch.repeat_interleave(torch.arange(n, device=dev), deg)
-        hist, bin_size = gdist.coarse_histogram(row_of, full.col.to(torch.int64), n, min(1024, n))
-        del row_of, deg
-        hist_np = hist.cpu().numpy()
-        bounds = gdist.lshape_bounds(hist_np, bin_size, n, world, row_weight=args.row_weight,
-                                     comm_weight=args.comm_weight)
-        if args.refine:
-            bounds, _pred = gdist.refine_lshape_bounds(hist_np, bin_size, n, bounds, d)
-    else:
-        rp = full.rowptr.cpu().numpy().astype(np.int64)
-        bounds = gdist.nnz_balanced_bounds(rp + (np.arange(len(rp)) * args.row_weight).astype(np.int64), world)
-    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
     gen = torch.Generator(device=dev).manual_seed(2)
     x_full = torch.randn(n, d, device=dev, generator=gen)                     # identical on every rank
-    y_full = full.spmm(x_full)
-    y_ref = y_full[lo:hi].clone()                                             # 1-GPU product, for the check below
-    t1a, t1b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize()
-    t1a.record()
-    for _ in range(3):
-        full.spmm(x_full, out=y_full)                                         # the same product on ONE GPU, timed
-    t1b.record()
-    torch.cuda.synchronize()
-    ms_1gpu = t1a.elapsed_time(t1b) / 3
-    del y_full
+    transport = args.transport
+    g2 = None
     if args.partition == "lshape":
-        transport = args.transport
         if transport == "p2p" and not gdist.p2p_available(dev):
             transport = "nccl"                      # no peer mapping on this box: NCCL all-to-all, two communicators
             args.two_comms = True
         g2 = dist.new_group(backend="nccl", pg_options=dist.ProcessGroupNCCL.Options(is_high_priority_stream=True)) \
             if (args.two_comms and transport == "nccl") else None
-        part = gdist.LShapedSpMM.from_full(full, bounds, rank, world, d, group_partials=g2, transport=transport,
-                                           push_ctas=args.push_ctas, hub_first=bool(args.hub_first),
-                                           split_pull=bool(args.split_pull))
+
+    def finish_ms(part, reps=3):
+        """Per-rank time from a common start until this rank's Y block is complete (waits on other ranks included)."""
+        for _ in range(2):
+            part.spmm(None)
+        ts = []
+        for _ in range(reps):
+            torch.cuda.synchronize()
+            dist.barrier()
+            a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a_.record()
+            part.spmm(None)
+            b_.record()
+            torch.cuda.synchronize()
+            ts.append(a_.elapsed_time(b_))
+        t = torch.tensor([float(np.median(ts))], device=dev, dtype=torch.float64)
+        out = [torch.zeros_like(t) for _ in range(world)]
+        dist.all_gather(out, t)
+        return np.array([float(o.item()) for o in out])
+
+    def partition_and_check(mat, tag):
+        """Bounds (+ measured rebalancing), the rank's partition object, the same product on ONE GPU (timed) and the
+        check of the partitioned product against it on every rank."""
+        hist_np = bin_size = None
+        rebal = {"iterations": 0}
+        if args.partition == "lshape":
+            deg = (mat.rowptr[1:] - mat.rowptr[:-1]).to(torch.int64)
+            row_of = torch.repeat_interleave(torch.arange(n, device=dev), deg)
+            hist, bin_size = gdist.coarse_histogram(row_of, mat.col.to(torch.int64), n, min(1024, n))
+            del row_of, deg
+            hist_np = hist.cpu().numpy()
+            del hist
+        y_full = mat.spmm(x_full)
+        t1a, t1b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        t1a.record()
+        for _ in range(3):
+            mat.spmm(x_full, out=y_full)                                      # the same product on ONE GPU, timed
+        t1b.record()
+        torch.cuda.synchronize()
+        ms_one = t1a.elapsed_time(t1b) / 3
+
+        def build(bounds):
+            if args.partition == "lshape":
+                pt = gdist.LShapedSpMM.from_full(mat, bounds, rank, world, d, group_partials=g2, transport=transport,
+                                                 push_ctas=args.push_ctas, hub_first=bool(args.hub_first),
+                                                 split_pull=bool(args.split_pull), fused_push=bool(args.fused_push))
+            else:
+                pt = gdist.RowPartitionedSpMM.from_full(mat, bounds, rank, world, d, overlap=not args.no_overlap)
+            pt.x_own.copy_(x_full[int(bounds[rank]):int(bounds[rank + 1])])
+            return pt
+
+        if args.partition == "lshape":
+            weights = np.ones(world)
+            history = []
+            for it in range(max(args.rebalance, 0) + 1):
+                bounds = gdist.lshape_bounds(hist_np, bin_size, n, world, row_weight=args.row_weight,
+                                             comm_weight=args.comm_weight, rank_weights=weights)
+                if args.refine and it == 0:
+                    bounds, _pred = gdist.refine_lshape_bounds(hist_np, bin_size, n, bounds, d)
+                part = build(bounds)
+                if it == max(args.rebalance, 0):
+                    break
+                t = finish_ms(part)                                           # identical array on every rank
+                history.append({"bounds": [int(b) for b in bounds], "finish_ms_per_rank": [round(float(v), 3) for v in t]})
+                weights = gdist.rebalance_weights(weights, t)
+                del part
+                torch.cuda.empty_cache()
+            rebal = {"iterations": len(history), "history": history, "rank_weights": [round(float(w), 4) for w in weights],
+                     "note": "bounds re-derived from the MEASURED per-rank finish time of a step (set-up, untimed)"}
+        else:
+            rp = mat.rowptr.cpu().numpy().astype(np.int64)
+            bounds = gdist.nnz_balanced_bounds(rp + (np.arange(len(rp)) * args.row_weight).astype(np.int64), world)
+            part = build(bounds)
+        lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+        y_ref = y_full[lo:hi].clone()
+        del y_full
+        torch.cuda.empty_cache()
+        # check against the 1-GPU product on EVERY rank (reduced below): the partitioned product differs from it only
+        # in fp32 summation order.  1st: the north_star tolerance (1e-5 rel / 1e-6 abs), as a fraction of the entries;
+        # 2nd, explicit and relaxed: fp32 sums of up to ~10^5 terms, bounded relative to the row block's largest entry.
+        y = part.spmm(None)
+        err = (y - y_ref).abs()
+        strict = (err <= 1e-6) | (err <= 1e-5 * y_ref.abs())
+        relaxed = strict | (err <= 4e-7 * y_ref.abs().max())
+        chk = torch.tensor([float(strict.double().mean().item()), float(relaxed.all().item()), -float(err.max().item())],
+                           device=dev, dtype=torch.float64)
+        dist.all_reduce(chk, op=dist.ReduceOp.MIN)                # worst rank
+        # a second step on CHANGED inputs: the exchange buffers must not leak rows of the previous step
+        part.x_own.mul_(-0.5)
+        y2 = part.spmm(None)
+        err2 = (y2 - (-0.5) * y_ref).abs()
+        ok2 = torch.tensor([float(((err2 <= 1e-6) | (err2 <= 1e-5 * y_ref.abs()) | (err2 <= 4e-7 * y_ref.abs().max()))
+                                  .all().item())], device=dev, dtype=torch.float64)
+        dist.all_reduce(ok2, op=dist.ReduceOp.MIN)
+        part.x_own.mul_(-2.0)
+        res = {"bounds": [int(b) for b in bounds], "ms_1gpu": ms_one, "strict_frac": float(chk[0].item()),
+               "tol_ok": bool(chk[1].item() > 0.5 and ok2.item() > 0.5), "max_err": -float(chk[2].item()),
+               "rebalance": rebal}
+        del y_ref, err, err2, y2, strict, relaxed
+        return part, res
+
+    def timed_steps(part):
+        for _ in range(args.warmup):
+            part.spmm(None)
+        torch.cuda.synchronize()
+        dist.barrier()
+        a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a_.record()
+        for _ in range(args.steps):
+            part.spmm(None)
+        b_.record()
+        torch.cuda.synchronize()
+        dist.barrier()
+        t = torch.tensor([a_.elapsed_time(b_) / args.steps], device=dev, dtype=torch.float64)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    # ---- the transposed product first (its objects are freed before the headline measurement) ---------------------
+    transposed = None
+    if args.transposed:
+        full_t = full.transpose()                                             # explicit second CSR (SURVEY 0.3)
+        full._t = None
+        full_t._t = None
+        part_t, res_t = partition_and_check(full_t, "transposed")
+        ms_t = timed_steps(part_t)
+        transposed = {"workload": "G_in = A_hat^T G (the backward aggregation, SURVEY 8e): a second L-shaped partition of the "
+                                  "explicit transposed CSR, same kernels and exchange",
+                      "ms_per_step": ms_t, "gedges_per_s": nnz_total / (ms_t * 1e-3) / 1e9,
+                      "same_product_on_1_gpu_ms": res_t["ms_1gpu"], "efficiency_vs_1gpu": res_t["ms_1gpu"] / (world * ms_t),
+                      "bounds": res_t["bounds"], "rebalance": res_t["rebalance"],
+                      "check_vs_1gpu_product": {"within_tolerance": res_t["tol_ok"], "max_abs_err": res_t["max_err"],
+                                                "strict_1e-5rel_1e-6abs_fraction_worst_rank": res_t["strict_frac"],
+                                                "ranks_checked": world}}
+        tol_ok_t = res_t["tol_ok"]
+        del part_t, full_t
+        torch.cuda.empty_cache()
     else:
-        part = gdist.RowPartitionedSpMM.from_full(full, bounds, rank, world, d, overlap=not args.no_overlap)
-    del full
-    part.x_own.copy_(x_full[lo:hi])
-    del x_full
+        tol_ok_t = True
+    part, res = partition_and_check(full, "forward")
+    bounds, ms_1gpu = res["bounds"], res["ms_1gpu"]
+    strict_frac, tol_ok, max_err = res["strict_frac"], res["tol_ok"] and tol_ok_t, res["max_err"]
+    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+    del full, x_full
     torch.cuda.empty_cache()
     x_local = None
-    # check against the 1-GPU product on EVERY rank (reduced below): the partitioned product differs from it only
-    # in fp32 summation order.  1st: the north_star tolerance (1e-5 rel / 1e-6 abs), as a fraction of the entries;
-    # 2nd, explicit and relaxed: fp32 sums of up to ~10^5 terms, bounded relative to the row block's largest entry.
-    y = part.spmm(x_local)
-    err = (y - y_ref).abs()
-    strict = (err <= 1e-6) | (err <= 1e-5 * y_ref.abs())
-    relaxed = strict | (err <= 4e-7 * y_ref.abs().max())
-    chk = torch.tensor([float(strict.double().mean().item()), float(relaxed.all().item()), -float(err.max().item())],
-                       device=dev, dtype=torch.float64)
-    dist.all_reduce(chk, op=dist.ReduceOp.MIN)                # worst rank
-    # a second step on CHANGED inputs: the exchange buffers must not leak rows of the previous step
-    part.x_own.mul_(-0.5)
-    y2 = part.spmm(x_local)
-    err2 = (y2 - (-0.5) * y_ref).abs()
-    ok2 = torch.tensor([float(((err2 <= 1e-6) | (err2 <= 1e-5 * y_ref.abs()) | (err2 <= 4e-7 * y_ref.abs().max()))
-                              .all().item())], device=dev, dtype=torch.float64)
-    dist.all_reduce(ok2, op=dist.ReduceOp.MIN)
-    part.x_own.mul_(-2.0)
-    strict_frac, tol_ok, max_err = float(chk[0].item()), bool(chk[1].item() > 0.5 and ok2.item() > 0.5), -float(chk[2].item())
-    del y_ref, err, err2, y2, strict, relaxed
     for _ in range(args.warmup):
         part.spmm(x_local)
     torch.cuda.synchronize()
@@ -587,8 +686,18 @@ def run_rmat_spmm_dist(args):
         if args.partition == "lshape":
             t_x = timed(part.exchange_x)
             nop = lambda: None                     # every rank must enter timed() (it holds a barrier)
-            t_push = timed(part.push_product)
-            t_p = timed(part.exchange_partials)
+
+            def fused_push_local():                # the fused push product with LOCAL outputs (compute share only)
+                for lo_, hi_, _v in part._push_ranges:
+                    part._push_product_rows(lo_, hi_, out=part._diag_psend[lo_:hi_])
+            if getattr(part, "fused_push", False):
+                part._diag_psend = torch.empty(part.n_psend, d, device=dev)
+                t_push = timed(fused_push_local)
+                t_p = 0.0
+                timed(nop)
+            else:
+                t_push = timed(part.push_product)
+                t_p = timed(part.exchange_partials)
             t_pull = timed(lambda: part.pull.spmm(part.xbuf, out=part.y))
             t_add = timed((lambda: part.add.spmm(part.precv, e1=part.y, out=part.y)) if part.n_precv else nop)
             t_all = timed(lambda: part.spmm(None))
@@ -675,6 +784,7 @@ def run_rmat_spmm_dist(args):
                        "same_product_on_1_gpu_ms": ms_1gpu,
                        "efficiency_vs_1gpu": ms_1gpu / (world * ms),          # E(p) = T(1) / (p T(p)), same process
                        "bounds": [int(b) for b in bounds], "row_weight": args.row_weight,
+                       "fused_push": bool(getattr(part, "fused_push", False)), "rebalance": res["rebalance"],
                        "hub_first": bool(getattr(part, "hub_first", False)),
                        "split_pull": bool(getattr(part, "_split_requested", False)),
                        "l2": "inputs larger than L2", "transport": part.transport,
@@ -686,7 +796,7 @@ def run_rmat_spmm_dist(args):
             "e2e": {"value": nnz_total / (e2e_ms * 1e-3) / 1e9, "unit": "GEdges/s", "ms_per_step": e2e_ms,
                     "steps": e2e_steps, "h2d_bytes_per_step": int(io[0].item()), "d2h_bytes_per_step": int(io[1].item()),
                     "note": "every rank uploads its X block from pinned host memory and downloads its Y block, each step"},
-            "gpu_launches": int(launches.item()), "clocks": clk,
+            "gpu_launches": int(launches.item()), "clocks": clk, "transposed": transposed,
             "roofline": {"kernel": "spmm_warp_row_kernel<float> (push + pull + add products of every rank) with the exchange "
                                    "(push_rows_kernel / NCCL) inside the step", "bound": "hbm",
                          "achieved": gbs, "peak": peak * world, "unit": "GB/s", "frac": gbs / (peak * world),

@@ -21,6 +21,7 @@ from . import synth  # noqa: F401
 from . import optim  # noqa: F401
 from . import textio  # noqa: F401
 from . import kipf  # noqa: F401
+from . import walker  # noqa: F401
 from .graph import DeviceCSR, device_csr_of  # noqa: F401
 from .model import GSS_GNNLayer, ResidualGraphConvolutionalNetwork, GSS_loss  # noqa: F401
 from .helper import (gen_graph, combine_graph, preprocess_graph,  # noqa: F401

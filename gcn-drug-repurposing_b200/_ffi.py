@@ -81,6 +81,9 @@ _SIGNATURES = {
     "gdr_masked_softmax_ce_workspace_bytes": (c_i64, [c_i64]),
     "gdr_masked_softmax_ce_f32": (c_i32, [c_ptr, c_i64, c_ptr, c_ptr, c_i64, c_i64, c_ptr, c_ptr, c_ptr, c_ptr, c_i64,
                                           c_ptr]),
+    "gdr_walk_row_cumsum_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_ptr, c_ptr]),
+    "gdr_node2vec_walks": (c_i32, [c_ptr, c_ptr, c_ptr, c_i64, c_ptr, c_i64, c_i64, c_f64, c_f64, c_i32, ctypes.c_uint64,
+                                   c_i64, c_ptr, c_ptr]),
     "gdr_text_savetxt_bytes": (c_i64, [c_i64, c_i64]),
     "gdr_text_savetxt_e18": (c_i64, [c_ptr, c_i64, c_i64, c_i32, ctypes.c_char_p, c_i64, c_i32]),
     "gdr_text_parse_embs": (c_i64, [ctypes.c_char_p, c_i64, c_i32, c_ptr, c_i64, c_ptr, c_ptr,

@@ -199,7 +199,7 @@ def coarse_histogram(row_global, col_global, n, bins):
     return torch.bincount(key, minlength=bins * bins).reshape(bins, bins), size
 
 
-def lshape_bounds(hist, bin_size, n, parts, row_weight=6.0, comm_weight=0.0):
+def lshape_bounds(hist, bin_size, n, parts, row_weight=6.0, comm_weight=0.0, rank_weights=None):
     """Bounds [parts+1] (multiples of bin_size, last = n) that minimise the largest L-shape cost
         cost(s) = nnz(L_s) + row_weight * (own rows + expected non-empty rows of the push blocks computed here
                                            + add pass: own rows + expected partial rows received)
@@ -208,9 +208,12 @@ def lshape_bounds(hist, bin_size, n, parts, row_weight=6.0, comm_weight=0.0):
     coarse histogram (rows of a bin hit by lambda entries each: non-empty fraction 1 - exp(-lambda)); for traffic
     towards the not-yet-placed higher ranks the remaining index range is taken as (parts - s - 1) equal chunks.
     comm_weight is in nnz-equivalents per row moved (a 512-byte row at ~750 GB/s costs ~14 gathers of ~50 ps).
+    rank_weights [parts]: multiplier on each rank's modelled cost (default 1).  The model knows nothing about who waits
+    for whom inside a step, so `rebalance_weights` feeds the MEASURED finish time of every rank back through it.
     hist: numpy [B, B] from coarse_histogram (summed over ranks)."""
     hist = np.asarray(hist, dtype=np.float64)
     nb = hist.shape[0]
+    rw = np.ones(parts) if rank_weights is None else np.asarray(rank_weights, dtype=np.float64)
     sq = np.zeros(nb + 1)
     sq[1:] = np.diagonal(hist.cumsum(0).cumsum(1))                      # nnz of the leading square [0,b)x[0,b)
     ccum = np.zeros((nb, nb + 1))
@@ -256,13 +259,13 @@ def lshape_bounds(hist, bin_size, n, parts, row_weight=6.0, comm_weight=0.0):
             if b >= nb:
                 out.append(nb)
                 continue
-            c = costs_from(b, s)
+            c = costs_from(b, s) * rw[s]
             k = int(np.searchsorted(c, cap, side="right"))               # number of end bins with cost <= cap
             b = b + max(k, 1)
             out.append(min(b, nb))
         return out
 
-    lo, hi = 0.0, float(costs_from(0, 0)[-1]) * 1.01 + 1.0
+    lo, hi = 0.0, float(costs_from(0, 0)[-1]) * float(rw.max()) * 1.01 + 1.0
     for _ in range(30):
         mid = 0.5 * (lo + hi)
         if fill(mid)[-1] >= nb:
@@ -272,6 +275,17 @@ def lshape_bounds(hist, bin_size, n, parts, row_weight=6.0, comm_weight=0.0):
     b = fill(hi)
     b[-1] = nb
     return np.minimum(np.asarray(b, dtype=np.int64) * bin_size, n)
+
+
+def rebalance_weights(weights, finish_ms, damping=0.8, clip=(0.25, 4.0)):
+    """New rank_weights for lshape_bounds from the measured per-rank finish times of a step (time from the common
+    start until the rank's Y block is complete, waits on other ranks' rows included): a rank that finishes late gets a
+    proportionally heavier cost, hence a smaller region.  Normalised to mean 1."""
+    w = np.asarray(weights, dtype=np.float64)
+    t = np.asarray(finish_ms, dtype=np.float64)
+    w = w * (t / t.mean()) ** damping
+    w = np.clip(w / w.mean(), clip[0], clip[1])
+    return w / w.mean()
 
 
 def csr_from_sorted_rows(row, col, val, n_rows, n_cols):
@@ -309,12 +323,17 @@ class LShapedSpMM:
     """
 
     def __init__(self, local_csr, bounds, rank, world, d, group=None, comm_stream=None, group_partials=None,
-                 transport="nccl", push_ctas=0, hub_first=False, split_pull=False):
+                 transport="nccl", push_ctas=0, hub_first=False, split_pull=False, fused_push=False):
         """group_partials: a second communicator for the partial-row exchange, so that it can run while the
         X-row exchange is still in flight (opposite directions on full-duplex links); default: `group`.
         transport: "nccl" (all_to_all of packed rows) or "p2p" (gdr_push_rows_f32: rows are stored straight into
         the destination's receive region over NVLink; buffers live in symmetric memory).
         p2p only (both change the order of launches, not the arithmetic of any output row's partial sums):
+          fused_push  the push product stores its output rows STRAIGHT into the destination's receive region (the SpMM
+                      kernel's row stores are peer stores over NVLink: 512 contiguous bytes per warp): one launch per
+                      destination, rank 0's block first.  No psend buffer, no second copy kernel, and the partial rows
+                      travel WHILE the product runs instead of after it — the partial exchange disappears from the
+                      step's critical path and its copy kernel no longer competes with the pull product for SMs.
           hub_first   the push product runs in two launches, the block whose partial rows go to rank 0 first, and
                       those rows leave as soon as it is done: rank 0 receives the most partial rows (its link is
                       the critical path of the partial exchange) and no longer waits for the whole push product.
@@ -384,7 +403,8 @@ class LShapedSpMM:
         f = dict(dtype=val.dtype, device=dev)
         self.p2p = transport == "p2p"
         self.push_ctas = int(push_ctas)
-        self.hub_first = bool(hub_first) and self.p2p and world > 2
+        self.fused_push = bool(fused_push) and self.p2p and world > 1
+        self.hub_first = bool(hub_first) and self.p2p and world > 2 and not self.fused_push
         self.split_pull = split_pull if (self.p2p and world > 1) else False
         self._split_requested = self.split_pull                           # same value on every rank
         self._push_slices = {}
@@ -397,7 +417,7 @@ class LShapedSpMM:
             self.xsend = torch.empty(int(self.send_idx.numel()), d, **f)
         self._pull_parts = self._add_parts = self._late_mask = None        # construction-time index lists
         self.x_own, self.x_recv = self.xbuf[:self.n_own], self.xbuf[self.n_own:]
-        self.psend = torch.empty(self.n_psend, d, **f)
+        self.psend = torch.empty(0 if self.fused_push else self.n_psend, d, **f)
         self.y = torch.empty(self.n_own, d, **f)
         self.recv_rows = n_xrecv + self.n_precv
         self.sent_rows = int(self.send_idx.numel()) + self.n_psend
@@ -407,7 +427,9 @@ class LShapedSpMM:
             self.comm_stream = torch.cuda.Stream(device=dev, priority=-1)
         self.comm_stream2 = (torch.cuda.Stream(device=dev, priority=-1)
                              if ((self.two_comms or self.p2p) and dev.type == "cuda") else self.comm_stream)
-        self.transport = ("p2p stores into peer symmetric memory (gdr_push_rows_f32) x2" if self.p2p else
+        self.transport = ("p2p: X rows by gdr_push_rows_f32, partial rows stored into peer memory by the push product itself"
+                          if self.fused_push else
+                          "p2p stores into peer symmetric memory (gdr_push_rows_f32) x2" if self.p2p else
                           "nccl all_to_all x2") + " (X rows to higher ranks, partial Y rows to lower ranks), L-shaped partition"
 
     def _setup_p2p(self, n_xrecv, f):
@@ -454,6 +476,13 @@ class LShapedSpMM:
         rest_cnt = [0] + pcnt[1:]
         self._ppush_hub = (arr(*pdst), arr(*([None] * world)), i64(*poff), i64(*hub_cnt))
         self._ppush_rest = (arr(*pdst), arr(*([None] * world)), i64(*poff), i64(*rest_cnt))
+        # fused push: the destination's receive slice as a local tensor over peer memory
+        self._push_ranges = []
+        if self.fused_push:
+            for a in range(world):
+                if pcnt[a]:
+                    view = self._hdl.get_buffer(a, (pcnt[a], d), f["dtype"], (xrows_max + sum(meta[a]["precv"][:s])) * d)
+                    self._push_ranges.append((poff[a], poff[a] + pcnt[a], view))
         self._xrows_max = xrows_max
         self._x_sources = [r for r in range(world) if self.xrecv_splits[r] > 0]
         self._x_dests = [r for r in range(world) if self.xsend_splits[r] > 0]
@@ -543,8 +572,9 @@ class LShapedSpMM:
         if self.n_psend:
             self.push.spmm(self.x_own, out=self.psend)                    # needs only the own X block
 
-    def _push_product_rows(self, lo, hi):
-        """Rows [lo, hi) of the push product (a row slice of the same CSR: same kernel, same per-row arithmetic)."""
+    def _push_product_rows(self, lo, hi, out=None):
+        """Rows [lo, hi) of the push product (a row slice of the same CSR: same kernel, same per-row arithmetic);
+        out: where the rows go (default: psend[lo:hi]; fused_push: the destination's receive slice, peer memory)."""
         if hi <= lo:
             return
         key = (lo, hi)
@@ -555,7 +585,7 @@ class LShapedSpMM:
             sub = DeviceCSR((rp[lo:hi + 1] - p0).contiguous(), self.push.col[p0:p1], self.push.val[p0:p1], hi - lo,
                             self.push.n_cols)
             self._push_slices[key] = sub
-        sub.spmm(self.x_own, out=self.psend[lo:hi])
+        sub.spmm(self.x_own, out=self.psend[lo:hi] if out is None else out)
 
     def hub_reduce(self):
         pass                                                              # (NvlsLShapedSpMM only)
@@ -580,7 +610,16 @@ class LShapedSpMM:
         cs.wait_stream(cur)
         with torch.cuda.stream(cs):
             ev_early, ev_late = self.exchange_x()
-        if self.hub_first and self.n_psend_hub and self.n_psend_hub < self.n_psend:
+        if self.fused_push:
+            cur.wait_event(self._ev_b0)                                   # every rank is done reading last step's precv
+            for lo_, hi_, view in self._push_ranges:                      # rank 0's block first: it receives the most
+                self._push_product_rows(lo_, hi_, out=view)
+            ev_p = cur.record_event()
+            with torch.cuda.stream(cs2):
+                cs2.wait_event(ev_p)
+                self._hdl.barrier(channel=2)                              # every rank's partial rows have landed
+                ev_y = cs2.record_event()
+        elif self.hub_first and self.n_psend_hub and self.n_psend_hub < self.n_psend:
             self._push_product_rows(0, self.n_psend_hub)                  # partial rows for rank 0 first ...
             ev_p0 = cur.record_event()
             with torch.cuda.stream(cs2):

@@ -268,6 +268,20 @@ int gdr_masked_softmax_ce_f32(const float *logits, int64_t ld, const float *labe
                               float *dlogits_out, void *workspace, int64_t workspace_bytes,
                               gdr_stream_t stream);
 
+/* ---- node2vec / DeepWalk walk generation (multiscale/openne/walker.py:11-161) ------------------------------- *
+ * CSR of the directed graph with ascending columns per row; cum = per-row running sums of the edge weights
+ * (gdr_walk_row_cumsum_f32; weight == NULL: all ones = BasicWalker's uniform choice).  One thread per walk:
+ * first-order draws by inverse CDF, second-order steps (second_order != 0) by rejection against max(1/p,1,1/q)
+ * with the reference's factors (1/p back to the previous node, 1 if next -> previous is an edge, 1/q otherwise).
+ * walks_out [n_walks, walk_length] int32 node indices, -1 after a walk ended at a node without out-neighbours.
+ * Random numbers: counter-based, a pure function of (seed, walk_id0 + walk, draw).                            */
+int gdr_walk_row_cumsum_f32(const int32_t *rowptr, const float *weight, int64_t n, float *cum_out,
+                            gdr_stream_t stream);
+int gdr_node2vec_walks(const int32_t *rowptr, const int32_t *col, const float *cum, int64_t n,
+                       const int32_t *start, int64_t n_walks, int64_t walk_length, double p, double q,
+                       int second_order, uint64_t seed, int64_t walk_id0, int32_t *walks_out,
+                       gdr_stream_t stream);
+
 /* ---- optimizer ------------------------------------------------------------------------ *
  * torch.optim.Adam single step (train.py:139,184), one launch for all tensors laid out
  * back to back in flat buffers of `count` floats; step_dev: device int32 counter that

@@ -48,7 +48,9 @@ def main():
         variants += [("p2p", dict(transport="p2p")),
                      ("p2p+hub_first", dict(transport="p2p", hub_first=True)),
                      ("p2p+split_pull", dict(transport="p2p", split_pull="force")),
-                     ("p2p+hub_first+split_pull", dict(transport="p2p", hub_first=True, split_pull="force"))]
+                     ("p2p+hub_first+split_pull", dict(transport="p2p", hub_first=True, split_pull="force")),
+                     ("p2p+fused_push", dict(transport="p2p", fused_push=True)),
+                     ("p2p+fused_push+split_pull", dict(transport="p2p", fused_push=True, split_pull="force"))]
     for name, kw in variants:
         part = gdist.LShapedSpMM.from_full(full, bounds, rank, world, d, **kw)
         if "split_pull" in kw and rank > 0:
@@ -61,7 +63,9 @@ def main():
             first = y.clone()
         assert torch.equal(part.spmm(xs[-1][lo:hi]), first), f"{name}: two steps on the same input differ"
         # the row-sliced push product (hub_first) is the same kernel on a row range: identical bits
-        if part.n_psend > 1:
+        if "fused_push" in kw:
+            assert part.fused_push and part.psend.numel() == 0, "fused_push was requested but not set up"
+        if part.n_psend > 1 and not part.fused_push:
             part.push_product()
             whole = part.psend.clone()
             mid = part.n_psend // 3
@@ -69,6 +73,22 @@ def main():
             part._push_product_rows(0, mid)
             part._push_product_rows(mid, part.n_psend)
             assert torch.equal(part.psend, whole), f"{name}: sliced push product differs"
+        torch.cuda.synchronize()
+        dist.barrier()
+        del part
+    # ---- the transposed product (backward aggregation A_hat^T G): a second partition of the explicit transpose, with
+    # bounds skewed by rank weights (what the measured rebalancing of bench.py produces) -------------------------
+    full_t = full.transpose()
+    deg_t = (full_t.rowptr[1:] - full_t.rowptr[:-1]).to(torch.int64)
+    row_t = torch.repeat_interleave(torch.arange(n, device=dev), deg_t)
+    hist_t, bs_t = gdist.coarse_histogram(row_t, full_t.col.to(torch.int64), n, min(1024, n))
+    w = gdist.rebalance_weights(np.ones(world), np.linspace(1.0, 2.0, world))
+    bounds_t = gdist.lshape_bounds(hist_t.cpu().numpy(), bs_t, n, world, row_weight=6.0, rank_weights=w)
+    lt, ht = int(bounds_t[rank]), int(bounds_t[rank + 1])
+    for name, kw in variants[:1] + variants[-2:-1]:
+        part = gdist.LShapedSpMM.from_full(full_t, bounds_t, rank, world, d, **kw)
+        for step, x in enumerate(xs[:2]):
+            close(part.spmm(x[lt:ht]), full_t.spmm(x)[lt:ht], f"transposed {name} step {step} rank {rank}")
         torch.cuda.synchronize()
         dist.barrier()
         del part

@@ -228,3 +228,23 @@ def test_step_model_and_refinement():
     assert abs(det["nnz_pull"].sum() + det["nnz_push"].sum() - m.nnz) < 1e-6 * m.nnz
     b1, t1 = gdist.refine_lshape_bounds(hist.numpy(), size, n, b0, 128, consts=dict(volume_scale=1.0))
     assert t1 <= t0 * (1 + 1e-9) and b1[0] == 0 and b1[-1] == n and (np.diff(b1) > 0).all()
+
+
+def test_lshape_bounds_follow_rank_weights():
+    """rank_weights (the measured-finish-time feedback of bench.py) shrink the region of a heavy rank and keep the
+    bounds a valid cover; rebalance_weights is normalised and monotone in the finish times."""
+    from gdr_b200 import dist as gdist
+    rng = np.random.default_rng(0)
+    nb, n = 64, 64 * 100
+    hist = rng.integers(50, 200, size=(nb, nb)).astype(np.float64)
+    hist[:8, :] *= 20
+    hist[:, :8] *= 20                                            # hub rows / columns, as on R-MAT
+    base = gdist.lshape_bounds(hist, 100, n, 4)
+    w = gdist.rebalance_weights(np.ones(4), [1.0, 1.0, 1.0, 2.0])
+    assert abs(w.mean() - 1.0) < 1e-12 and w[3] > w[0] and np.all(np.diff(w[:3]) == 0)
+    skew = gdist.lshape_bounds(hist, 100, n, 4, rank_weights=w)
+    for b in (base, skew):
+        assert b[0] == 0 and b[-1] == n and np.all(np.diff(b) >= 0)
+    assert (skew[4] - skew[3]) < (base[4] - base[3])             # the slow last rank gets fewer rows
+    same = gdist.lshape_bounds(hist, 100, n, 4, rank_weights=np.ones(4))
+    assert np.array_equal(same, base)
