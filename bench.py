@@ -46,8 +46,8 @@ L2_FLUSH_BYTES = 256 << 20
 DIST_ROW_WEIGHT = 6.0
 DIST_HUB_FIRST = 0
 DIST_SPLIT_PULL = 0
-DIST_FUSED_PUSH = 1          # the push product stores its partial rows straight into peer memory
-DIST_REBALANCE = 2           # rounds of measured-finish-time rebalancing of the L-shape bounds at set-up
+DIST_FUSED_PUSH = 0          # measured at N = 8: the incast on rank 0 stalls every sender's push product (10.0 vs 7.4 ms)
+DIST_REBALANCE = 0           # measured at N = 8 (profiles/sweep_r2b_n8_lshape_options.jsonl): ranks are coupled through the step's barriers, finish-time feedback does not help (7.8 vs 7.3 ms)
 # L2 -> SM peak: ~6,300 bytes per clock for the whole chip (B300_MICROARCH.md, "LTS throughput cap", measured on
 # B300; no L2 figure in MEASURED_PEAKS.json), times the SM clock sampled during the run
 L2_BYTES_PER_CLK = 6300.0

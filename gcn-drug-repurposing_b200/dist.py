@@ -323,7 +323,7 @@ class LShapedSpMM:
     """
 
     def __init__(self, local_csr, bounds, rank, world, d, group=None, comm_stream=None, group_partials=None,
-                 transport="nccl", push_ctas=0, hub_first=False, split_pull=False, fused_push=False):
+                 transport="nccl", push_ctas=0, hub_first=False, split_pull=False, fused_push=False, x_priority=0):
         """group_partials: a second communicator for the partial-row exchange, so that it can run while the
         X-row exchange is still in flight (opposite directions on full-duplex links); default: `group`.
         transport: "nccl" (all_to_all of packed rows) or "p2p" (gdr_push_rows_f32: rows are stored straight into
@@ -334,6 +334,12 @@ class LShapedSpMM:
                       destination, rank 0's block first.  No psend buffer, no second copy kernel, and the partial rows
                       travel WHILE the product runs instead of after it — the partial exchange disappears from the
                       step's critical path and its copy kernel no longer competes with the pull product for SMs.
+          x_priority  K > 0: ranks 0..K-1 (the hub ranks: they send the most X rows and are the last senders to finish)
+                      push their X rows one destination at a time, HIGHEST rank first, and raise that destination's
+                      arrival signal at once; every other rank keeps the single launch that serves all destinations
+                      in proportion.  The last ranks (most rows, longest pull product) then hold all their X rows
+                      when the second-largest sender is done instead of when rank 0 is.  Arrival is signalled per
+                      source (put/wait_signal) instead of by one barrier.
           hub_first   the push product runs in two launches, the block whose partial rows go to rank 0 first, and
                       those rows leave as soon as it is done: rank 0 receives the most partial rows (its link is
                       the critical path of the partial exchange) and no longer waits for the whole push product.
@@ -403,6 +409,7 @@ class LShapedSpMM:
         f = dict(dtype=val.dtype, device=dev)
         self.p2p = transport == "p2p"
         self.push_ctas = int(push_ctas)
+        self.x_priority = int(x_priority) if (transport == "p2p" and world > 1) else 0
         self.fused_push = bool(fused_push) and self.p2p and world > 1
         self.hub_first = bool(hub_first) and self.p2p and world > 2 and not self.fused_push
         self.split_pull = split_pull if (self.p2p and world > 1) else False
@@ -462,6 +469,12 @@ class LShapedSpMM:
                 xcnt[r] = c
             off += c
         self._xpush = (arr(*xdst), arr(*xidx), i64(*([0] * world)), i64(*xcnt))
+        self._xpush_one = {}
+        for r in range(world):
+            if xcnt[r]:
+                one = [0] * world
+                one[r] = xcnt[r]
+                self._xpush_one[r] = (arr(*xdst), arr(*xidx), i64(*([0] * world)), i64(*one))
         # partial rows: to every a < s, contiguous slices of psend, into a's precv after the rows of ranks < s
         pdst, pcnt, poff, off = [None] * world, [0] * world, [0] * world, 0
         for a in range(world):
@@ -539,6 +552,20 @@ class LShapedSpMM:
             cur = torch.cuda.current_stream()
             self._hdl.barrier(channel=0)            # every rank is done reading last step's xbuf / precv
             self._ev_b0 = cur.record_event()
+            if self.x_priority:
+                if self.rank < self.x_priority:
+                    for r in sorted(self._x_dests, reverse=True):      # one destination at a time, highest first
+                        self._push(self.x_own, self._xpush_one[r])
+                        self._hdl.put_signal(r, channel=self.SIG_X)
+                else:
+                    if self.send_idx.numel():
+                        self._push(self.x_own, self._xpush)
+                    for r in self._x_dests:
+                        self._hdl.put_signal(r, channel=self.SIG_X)
+                for r in self._x_sources:
+                    self._hdl.wait_signal(r, channel=self.SIG_X)
+                ev = cur.record_event()
+                return ev, ev
             if self.send_idx.numel():
                 self._push(self.x_own, self._xpush)
             if self._signals:

@@ -72,11 +72,41 @@ def main():
         kv = dict(item.split("=") for item in spec.split(","))
         rw, cw = float(kv.get("rw", 6)), float(kv.get("cw", 0))
         hf, sp, ctas = bool(int(kv.get("hf", 0))), bool(int(kv.get("sp", 0))), int(kv.get("ctas", 0))
-        bounds = gdist.lshape_bounds(hist_np, bin_size, n, world, row_weight=rw, comm_weight=cw)
-        lo, hi = int(bounds[rank]), int(bounds[rank + 1])
-        part = gdist.LShapedSpMM.from_full(full, bounds, rank, world, d, transport="p2p", push_ctas=ctas,
-                                           hub_first=hf, split_pull=sp)
-        part.x_own.copy_(x_full[lo:hi])
+        fp, xp, reb = bool(int(kv.get("fp", 0))), int(kv.get("xp", 0)), int(kv.get("reb", 0))
+
+        def finish_ms(pt, reps=3):
+            for _ in range(2):
+                pt.spmm(None)
+            ts = []
+            for _ in range(reps):
+                torch.cuda.synchronize()
+                dist.barrier()
+                a_, b_ = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                a_.record()
+                pt.spmm(None)
+                b_.record()
+                torch.cuda.synchronize()
+                ts.append(a_.elapsed_time(b_))
+            t = torch.tensor([float(np.median(ts))], device=dev, dtype=torch.float64)
+            out = [torch.zeros_like(t) for _ in range(world)]
+            dist.all_gather(out, t)
+            return np.array([float(o.item()) for o in out])
+
+        weights = np.ones(world)
+        history = []
+        for it in range(reb + 1):
+            bounds = gdist.lshape_bounds(hist_np, bin_size, n, world, row_weight=rw, comm_weight=cw, rank_weights=weights)
+            lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+            part = gdist.LShapedSpMM.from_full(full, bounds, rank, world, d, transport="p2p", push_ctas=ctas,
+                                               hub_first=hf, split_pull=sp, fused_push=fp, x_priority=xp)
+            part.x_own.copy_(x_full[lo:hi])
+            fin = finish_ms(part)
+            history.append([round(float(v), 2) for v in fin])
+            if it == reb:
+                break
+            weights = gdist.rebalance_weights(weights, fin)
+            del part
+            torch.cuda.empty_cache()
         y = part.spmm(None)
         ref = y_full[lo:hi]
         err = (y - ref).abs()
@@ -88,7 +118,7 @@ def main():
         for _ in range(args.warmup):
             part.spmm(None)
         ms, _ = timed(lambda: part.spmm(None), args.steps)
-        if args.diag:
+        if args.diag and not fp:
             nop = lambda: None  # noqa: E731
             _, t_x = timed(part.exchange_x, 5)
             _, t_push = timed(part.push_product, 5)
@@ -112,6 +142,7 @@ def main():
             print(json.dumps({"config": spec, "n_gpus": world, "scale": args.scale, "d": d, "ms_per_step": ms,
                               "same_product_on_1_gpu_ms": ms1, "efficiency_vs_1gpu": ms1 / (world * ms),
                               "gedges_per_s": full.nnz / (ms * 1e-3) / 1e9, "bounds": [int(v) for v in bounds],
+                              "finish_ms_per_rank_by_rebalance_round": history,
                               "strict_fraction_worst_rank": float(chk[0].item()),
                               "within_tolerance_all_ranks": bool(chk[1].item() > 0.5)}), flush=True)
         del part, y

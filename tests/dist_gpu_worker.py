@@ -49,6 +49,7 @@ def main():
                      ("p2p+hub_first", dict(transport="p2p", hub_first=True)),
                      ("p2p+split_pull", dict(transport="p2p", split_pull="force")),
                      ("p2p+hub_first+split_pull", dict(transport="p2p", hub_first=True, split_pull="force")),
+                     ("p2p+x_priority", dict(transport="p2p", x_priority=1)),
                      ("p2p+fused_push", dict(transport="p2p", fused_push=True)),
                      ("p2p+fused_push+split_pull", dict(transport="p2p", fused_push=True, split_pull="force"))]
     for name, kw in variants:
