@@ -347,17 +347,15 @@ def run_msi_gcn(args):
     h2d = d2h = 0
 
     def e2e_epoch(ep, count):
+        """Host buffers through the public call (trainer.GCNTrainer.epoch_from_host): per iteration the index batch and
+        the feature matrix are uploaded from pinned memory (train.py:157-160 moves both every iteration) and the loss
+        is read back; the upload of the next iteration overlaps the current one on a copy stream."""
         nonlocal h2d, d2h
-        loss_val = None
-        for b in ep:
-            bd = b.to(dev, non_blocking=True)
-            xd = feats_pinned.to(dev, non_blocking=True)             # train.py:159 re-uploads the features
-            loss = tr.iteration(bd, features=xd)
-            loss_val = loss.item()                                   # D2H read of the step result
-            if count:
-                h2d += b.numel() * 8 + feats_pinned.numel() * 4
-                d2h += 4
-        return loss_val
+        losses = tr.epoch_from_host(ep, feats_pinned)
+        if count:
+            h2d += sum(b.numel() * 8 for b in ep) + len(ep) * feats_pinned.numel() * 4
+            d2h += 4 * len(ep)
+        return losses[-1] if losses else None
 
     for ep in e2e_batches[:args.warmup]:
         e2e_epoch(ep, False)

@@ -112,6 +112,43 @@ class GCNTrainer:
             loss = self.iteration(b)
         return loss
 
+    def epoch_from_host(self, batches, features_host):
+        """One epoch of train.py:155-184 with HOST inputs, moved as the reference moves them — the index batch AND the
+        whole feature matrix go to the device in every iteration (train.py:157-160) and the loss is read back — but
+        with the upload of iteration i+1 running on a copy stream, into the other of two device buffers, while
+        iteration i computes.  batches: list of int64 CPU index tensors (pinned for asynchronous copies);
+        features_host: [N, d] fp32 CPU tensor (pinned).  Returns the list of loss values."""
+        dev = self.device
+        cur = torch.cuda.current_stream(dev)
+        if getattr(self, "_copy_stream", None) is None:
+            self._copy_stream = torch.cuda.Stream(device=dev)
+            self._feat_bufs = [torch.empty(features_host.shape, dtype=torch.float32, device=dev) for _ in range(2)]
+            self._buf_free = [None, None]
+        cs = self._copy_stream
+
+        def upload(i):
+            with torch.cuda.stream(cs):
+                if self._buf_free[i % 2] is not None:
+                    cs.wait_event(self._buf_free[i % 2])       # the iteration that read this buffer has finished
+                else:
+                    cs.wait_stream(cur)
+                self._feat_bufs[i % 2].copy_(features_host, non_blocking=True)
+                bd = batches[i].to(dev, non_blocking=True)
+                return bd, cs.record_event()
+
+        losses = []
+        nxt = upload(0) if batches else None
+        for i in range(len(batches)):
+            bd, ev = nxt
+            if i + 1 < len(batches):
+                nxt = upload(i + 1)
+            cur.wait_event(ev)
+            bd.record_stream(cur)
+            loss = self.iteration(bd, features=self._feat_bufs[i % 2])
+            self._buf_free[i % 2] = cur.record_event()
+            losses.append(loss.item())                         # device -> host read of the step's result
+        return losses
+
 
 def main(args):
     """train.py:72-193."""

@@ -416,3 +416,33 @@ def test_spmm_hub_rows_are_split_deterministically(gdr, d):
     got_t = csr.transpose().spmm(xd).cpu().numpy()           # columns 0..: transposed rows are short here
     ref_t = torch.sparse.mm(adj_cpu.t(), x).numpy()
     assert_close(got_t, ref_t, rtol=1e-5, atol=2e-6, what="hub spmm transposed")
+
+
+def test_epoch_from_host_matches_synchronous_uploads(gdr):
+    """trainer.GCNTrainer.epoch_from_host (uploads of iteration i+1 overlapped with iteration i on a copy stream, two
+    device buffers) must give exactly the losses and weights of the plain loop that uploads, then computes."""
+    from gdr_b200 import trainer as trainer_mod
+    n, d = 1500, 128
+    rng = np.random.default_rng(0)
+    a = sp.random(n, n, density=0.01, random_state=rng, format="csr")
+    a = (a + a.T).tocsr()
+    adj = gdr.convert_sparse_matrix_to_sparse_tensor(gdr.preprocess_graph(a))
+    feats = gdr.synth.synth_embeddings(n, d, seed=3)
+    gen = torch.Generator().manual_seed(5)
+    batches = [torch.randperm(n, generator=gen)[:256] for _ in range(7)]
+    out = []
+    for mode in ("sync", "pipelined"):
+        np.random.seed(2)
+        torch.manual_seed(2)
+        tr = trainer_mod.GCNTrainer(feats, adj, hidden_units=d, num_layers=2, layer_decay=0.3, lr=3e-4, batch_size=256,
+                                    beta=0.2, device="cuda:0")
+        if mode == "sync":
+            x = torch.from_numpy(feats)
+            losses = [tr.iteration(b.cuda(), features=x.cuda()).item() for b in batches]
+        else:
+            losses = tr.epoch_from_host([b.pin_memory() for b in batches], torch.from_numpy(feats).pin_memory())
+            losses += tr.epoch_from_host([], torch.from_numpy(feats).pin_memory())      # empty epoch: no-op
+        out.append((losses, [p.detach().cpu().clone() for p in tr.model.parameters()]))
+    assert out[0][0] == out[1][0], (out[0][0], out[1][0])
+    for p, q in zip(out[0][1], out[1][1]):
+        assert torch.equal(p, q)
