@@ -47,6 +47,7 @@ DIST_ROW_WEIGHT = 6.0
 DIST_HUB_FIRST = 0
 DIST_SPLIT_PULL = 0
 DIST_FUSED_PUSH = 0          # measured at N = 8: the incast on rank 0 stalls every sender's push product (10.0 vs 7.4 ms)
+DIST_VBLOCKS_AT_8 = 16       # cyclic virtual-block layout at 8 GPUs: 6.69 ms vs 7.38 ms (profiles/sweep_r2d_n8_lshape_cyclic.jsonl)
 DIST_REBALANCE = 0           # measured at N = 8 (profiles/sweep_r2b_n8_lshape_options.jsonl): ranks are coupled through the step's barriers, finish-time feedback does not help (7.8 vs 7.3 ms)
 # L2 -> SM peak: ~6,300 bytes per clock for the whole chip (B300_MICROARCH.md, "LTS throughput cap", measured on
 # B300; no L2 figure in MEASURED_PEAKS.json), times the SM clock sampled during the run
@@ -80,6 +81,8 @@ def parse_args():
                    help="N>1, p2p: the push product stores its rows straight into the destination's receive region")
     p.add_argument("--rebalance", type=int, default=DIST_REBALANCE,
                    help="N>1, lshape: rounds of bounds refinement from the measured per-rank finish times (set-up)")
+    p.add_argument("--vblocks", type=int, default=-1,
+                   help="N>1, lshape: virtual blocks per rank, owned cyclically (0: plain L-shape; -1: 16 at 8 GPUs, else 0)")
     p.add_argument("--transposed", type=int, default=1, help="N>1: also measure A_hat^T G (second partition)")
     p.add_argument("--refine", action="store_true",
                    help="N>1, lshape: descend on the step timeline model from the cost-cap bounds (measured: no gain "
@@ -540,6 +543,10 @@ def run_rmat_spmm_dist(args):
         dist.all_gather(out, t)
         return np.array([float(o.item()) for o in out])
 
+    vblocks = args.vblocks if args.vblocks >= 0 else (DIST_VBLOCKS_AT_8 if world >= 8 else 0)
+    if transport != "p2p" and args.vblocks < 0:
+        vblocks = 0                                  # measured on the peer-store transport only
+
     def partition_and_check(mat, tag):
         """Bounds (+ measured rebalancing), the rank's partition object, the same product on ONE GPU (timed) and the
         check of the partitioned product against it on every rank."""
@@ -572,7 +579,19 @@ def run_rmat_spmm_dist(args):
             pt.x_own.copy_(x_full[int(bounds[rank]):int(bounds[rank + 1])])
             return pt
 
-        if args.partition == "lshape":
+        rows_sel = None
+        if args.partition == "lshape" and vblocks > 0:
+            # cyclic ownership of world * vblocks virtual L-shapes (hub blocks spread over all NVLink ports)
+            vbounds = gdist.lshape_bounds(hist_np, bin_size, n, world * vblocks, row_weight=args.row_weight,
+                                          comm_weight=args.comm_weight)
+            part = gdist.LShapedSpMM.from_full_cyclic(mat, vbounds, rank, world, d, group_partials=g2, transport=transport,
+                                                      push_ctas=args.push_ctas or 64, fused_push=bool(args.fused_push))
+            rows_sel = part.rows_old
+            part.x_own.copy_(x_full[rows_sel])
+            bounds = [int(b) for b in part.bounds]
+            rebal = {"iterations": 0, "virtual_blocks_per_rank": vblocks,
+                     "virtual_block_bounds_natural_order": [int(b) for b in vbounds]}
+        elif args.partition == "lshape":
             weights = np.ones(world)
             history = []
             for it in range(max(args.rebalance, 0) + 1):
@@ -595,7 +614,7 @@ def run_rmat_spmm_dist(args):
             bounds = gdist.nnz_balanced_bounds(rp + (np.arange(len(rp)) * args.row_weight).astype(np.int64), world)
             part = build(bounds)
         lo, hi = int(bounds[rank]), int(bounds[rank + 1])
-        y_ref = y_full[lo:hi].clone()
+        y_ref = (y_full[lo:hi] if rows_sel is None else y_full[rows_sel]).clone()
         del y_full
         torch.cuda.empty_cache()
         # check against the 1-GPU product on EVERY rank (reduced below): the partitioned product differs from it only
@@ -778,11 +797,12 @@ def run_rmat_spmm_dist(args):
                                    "(BASELINE configs[4])"
                                    % (args.rmat_scale, args.rmat_edge_factor, d),
                        "nodes": n, "nnz": nnz_total, "d": d,
-                       "parallelism": f"{'L-shaped' if args.partition == 'lshape' else 'row'}-partition x{world}",
+                       "parallelism": f"{'L-shaped' if args.partition == 'lshape' else 'row'}-partition x{world}" + (f", {vblocks} virtual blocks per rank owned cyclically" if vblocks else ""),
                        "same_product_on_1_gpu_ms": ms_1gpu,
                        "efficiency_vs_1gpu": ms_1gpu / (world * ms),          # E(p) = T(1) / (p T(p)), same process
                        "bounds": [int(b) for b in bounds], "row_weight": args.row_weight,
                        "fused_push": bool(getattr(part, "fused_push", False)), "rebalance": res["rebalance"],
+                       "cyclic_virtual_blocks_per_rank": vblocks,
                        "hub_first": bool(getattr(part, "hub_first", False)),
                        "split_pull": bool(getattr(part, "_split_requested", False)),
                        "l2": "inputs larger than L2", "transport": part.transport,

@@ -308,6 +308,33 @@ def _a2a_var(t, send_splits, group):
     return out, recv_splits
 
 
+def cyclic_vblock_layout(vb, world):
+    """Cyclic ownership of V = world * m VIRTUAL blocks.  vb: bounds [V+1] of the virtual blocks in the natural vertex
+    order (lshape_bounds(..., parts=V): equal L-shape costs); virtual block k belongs to rank k % world.  Every rank then
+    owns a hub-like block, m - 2 middle ones and a tail-like one, so the X rows and partial rows that the plain L-shape
+    funnels through rank 0's NVLink port (2.2 GB each way per step on R-MAT-24) are spread over all ports.
+    Vertices are renumbered so that a rank's blocks are contiguous (rank r: blocks r, r + world, r + 2 world, ...).
+    Returns (order: virtual block id of the q-th block in the new numbering, new_vb: its bounds [V+1] in the new
+    numbering, rank_bounds [world+1])."""
+    vb = np.asarray(vb, dtype=np.int64)
+    v = len(vb) - 1
+    if v % world:
+        raise ValueError(f"cyclic_vblock_layout: {v} virtual blocks do not divide over {world} ranks")
+    m = v // world
+    order = np.array([t * world + r for r in range(world) for t in range(m)], dtype=np.int64)
+    sizes = vb[order + 1] - vb[order]
+    new_vb = np.concatenate([[0], np.cumsum(sizes)]).astype(np.int64)
+    return order, new_vb, new_vb[::m].copy()
+
+
+def cyclic_permutation(vb, order, device):
+    """perm[new id] = old id for the layout above, and its inverse (int64 device tensors)."""
+    perm = torch.cat([torch.arange(int(vb[k]), int(vb[k + 1]), device=device, dtype=torch.int64) for k in order])
+    inv = torch.empty_like(perm)
+    inv[perm] = torch.arange(perm.numel(), device=device, dtype=torch.int64)
+    return perm, inv
+
+
 class LShapedSpMM:
     """Rank s's share of Y = Â·X under the L-shaped partition (see the comment above).  Construct from the
     rank's ROW block (global column ids); the entries above the diagonal are redistributed to their column
@@ -323,12 +350,19 @@ class LShapedSpMM:
     """
 
     def __init__(self, local_csr, bounds, rank, world, d, group=None, comm_stream=None, group_partials=None,
-                 transport="nccl", push_ctas=0, hub_first=False, split_pull=False, fused_push=False, x_priority=0):
+                 transport="nccl", push_ctas=0, hub_first=False, split_pull=False, fused_push=False, x_priority=0,
+                 vblock_bounds=None, vblock_ids=None):
         """group_partials: a second communicator for the partial-row exchange, so that it can run while the
         X-row exchange is still in flight (opposite directions on full-duplex links); default: `group`.
         transport: "nccl" (all_to_all of packed rows) or "p2p" (gdr_push_rows_f32: rows are stored straight into
         the destination's receive region over NVLink; buffers live in symmetric memory).
         p2p only (both change the order of launches, not the arithmetic of any output row's partial sums):
+          (any transport) vblock_bounds / vblock_ids: the cyclic virtual-block layout (cyclic_vblock_layout): bounds of
+                      the virtual blocks in THIS numbering and their ids in the natural (hub-first) order.  The rule
+                      "block (a, b) is computed by the owner of max(a, b)" is then applied to virtual blocks: an
+                      entry (i, j) whose column lives on another rank is multiplied there (push) iff j's virtual
+                      block comes after i's, else its X row is pulled.  Every pair of ranks exchanges in both
+                      directions.
           fused_push  the push product stores its output rows STRAIGHT into the destination's receive region (the SpMM
                       kernel's row stores are peer stores over NVLink: 512 contiguous bytes per warp): one launch per
                       destination, rank 0's block first.  No psend buffer, no second copy kernel, and the partial rows
@@ -364,8 +398,18 @@ class LShapedSpMM:
         owner = torch.searchsorted(bnd, col, right=True) - 1
         val = local_csr.val
 
-        # ---- pull part: columns owned by ranks <= s ----------------------------------------------------
-        keep = owner <= s
+        # ---- pull part: columns owned by ranks <= s (virtual-block layout: own columns and earlier blocks) ---------
+        self.cyclic = vblock_bounds is not None
+        if self.cyclic:
+            vbnd = torch.as_tensor(np.asarray(vblock_bounds), dtype=torch.int64, device=dev)
+            vid = torch.as_tensor(np.asarray(vblock_ids), dtype=torch.int64, device=dev)
+            nvb = vid.numel()
+            k_col = vid[torch.clamp(torch.searchsorted(vbnd, col, right=True) - 1, 0, nvb - 1)]
+            k_row = vid[torch.clamp(torch.searchsorted(vbnd, row + lo, right=True) - 1, 0, nvb - 1)]
+            keep = (owner == s) | (k_col < k_row)
+            del k_col, k_row
+        else:
+            keep = owner <= s
         kcol, krow, kval = col[keep], row[keep], val[keep]
         need_from, new_col, _ = plan_exchange(kcol, self.bounds, s)       # owners > s get empty lists
         self.xrecv_splits = [int(t.numel()) for t in need_from]
@@ -409,10 +453,10 @@ class LShapedSpMM:
         f = dict(dtype=val.dtype, device=dev)
         self.p2p = transport == "p2p"
         self.push_ctas = int(push_ctas)
-        self.x_priority = int(x_priority) if (transport == "p2p" and world > 1) else 0
+        self.x_priority = int(x_priority) if (transport == "p2p" and world > 1 and vblock_bounds is None) else 0
         self.fused_push = bool(fused_push) and self.p2p and world > 1
-        self.hub_first = bool(hub_first) and self.p2p and world > 2 and not self.fused_push
-        self.split_pull = split_pull if (self.p2p and world > 1) else False
+        self.hub_first = bool(hub_first) and self.p2p and world > 2 and not self.fused_push and not self.cyclic
+        self.split_pull = split_pull if (self.p2p and world > 1 and not self.cyclic) else False
         self._split_requested = self.split_pull                           # same value on every rank
         self._push_slices = {}
         if self.p2p:
@@ -541,6 +585,38 @@ class LShapedSpMM:
         local = DeviceCSR((full_csr.rowptr[lo:hi + 1] - p0).contiguous(), full_csr.col[p0:p1].clone(),
                           full_csr.val[p0:p1].clone(), hi - lo, full_csr.n_cols)
         return cls(local, bounds, rank, world, d, group, group_partials=group_partials, **kw)
+
+    @classmethod
+    def from_full_cyclic(cls, full_csr, vb, rank, world, d, group=None, group_partials=None, **kw):
+        """Partition of `full_csr` (natural vertex order) under the cyclic virtual-block layout of `vb`
+        (cyclic_vblock_layout).  The object works in the renumbered order: `rows_old` holds the natural ids of this
+        rank's rows — x_own = X[rows_old], and spmm() returns (A X)[rows_old]."""
+        dev = full_csr.device
+        order, new_vb, rank_bounds = cyclic_vblock_layout(vb, world)
+        perm, inv = cyclic_permutation(vb, order, dev)
+        lo, hi = int(rank_bounds[rank]), int(rank_bounds[rank + 1])
+        rows_old = perm[lo:hi]
+        rp = full_csr.rowptr.to(torch.int64)
+        deg = rp[rows_old + 1] - rp[rows_old]
+        rowptr = torch.zeros(hi - lo + 1, dtype=torch.int64, device=dev)
+        rowptr[1:] = torch.cumsum(deg, 0)
+        nnz = int(rowptr[-1].item())
+        # entries of the gathered rows: position = start of the old row + offset inside the row
+        row_new = torch.repeat_interleave(torch.arange(hi - lo, device=dev), deg)
+        src = rp[rows_old][row_new] + (torch.arange(nnz, device=dev) - rowptr[:-1][row_new])
+        col = inv[full_csr.col[src].to(torch.int64)]
+        val = full_csr.val[src]
+        del src
+        key = row_new * int(rank_bounds[-1]) + col              # ascending new column ids inside every row
+        o = torch.argsort(key)
+        del key, row_new
+        local = DeviceCSR(rowptr.to(torch.int32), col[o].to(torch.int32).contiguous(), val[o].contiguous(), hi - lo,
+                          full_csr.n_cols)
+        del col, val, o
+        part = cls(local, rank_bounds, rank, world, d, group, group_partials=group_partials, vblock_bounds=new_vb,
+                   vblock_ids=order, **kw)
+        part.rows_old = rows_old
+        return part
 
     # the two exchanges, separately callable (tests replace the device products around them)
     SIG_X = 4                                       # signal-pad channel of the per-source X arrival flags

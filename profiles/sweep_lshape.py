@@ -73,6 +73,7 @@ def main():
         rw, cw = float(kv.get("rw", 6)), float(kv.get("cw", 0))
         hf, sp, ctas = bool(int(kv.get("hf", 0))), bool(int(kv.get("sp", 0))), int(kv.get("ctas", 0))
         fp, xp, reb = bool(int(kv.get("fp", 0))), int(kv.get("xp", 0)), int(kv.get("reb", 0))
+        vbm = int(kv.get("vb", 0))                       # cyclic layout: virtual blocks per rank (0: plain L-shape)
 
         def finish_ms(pt, reps=3):
             for _ in range(2):
@@ -95,11 +96,20 @@ def main():
         weights = np.ones(world)
         history = []
         for it in range(reb + 1):
-            bounds = gdist.lshape_bounds(hist_np, bin_size, n, world, row_weight=rw, comm_weight=cw, rank_weights=weights)
-            lo, hi = int(bounds[rank]), int(bounds[rank + 1])
-            part = gdist.LShapedSpMM.from_full(full, bounds, rank, world, d, transport="p2p", push_ctas=ctas,
-                                               hub_first=hf, split_pull=sp, fused_push=fp, x_priority=xp)
-            part.x_own.copy_(x_full[lo:hi])
+            if vbm:
+                bounds = gdist.lshape_bounds(hist_np, bin_size, n, world * vbm, row_weight=rw, comm_weight=cw)
+                part = gdist.LShapedSpMM.from_full_cyclic(full, bounds, rank, world, d, transport="p2p", push_ctas=ctas,
+                                                          fused_push=fp)
+                rows_sel = part.rows_old
+                part.x_own.copy_(x_full[rows_sel])
+            else:
+                bounds = gdist.lshape_bounds(hist_np, bin_size, n, world, row_weight=rw, comm_weight=cw,
+                                             rank_weights=weights)
+                lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+                part = gdist.LShapedSpMM.from_full(full, bounds, rank, world, d, transport="p2p", push_ctas=ctas,
+                                                   hub_first=hf, split_pull=sp, fused_push=fp, x_priority=xp)
+                rows_sel = slice(lo, hi)
+                part.x_own.copy_(x_full[lo:hi])
             fin = finish_ms(part)
             history.append([round(float(v), 2) for v in fin])
             if it == reb:
@@ -108,7 +118,7 @@ def main():
             del part
             torch.cuda.empty_cache()
         y = part.spmm(None)
-        ref = y_full[lo:hi]
+        ref = y_full[rows_sel]
         err = (y - ref).abs()
         strict = (err <= 1e-6) | (err <= 1e-5 * ref.abs())
         ok = bool((strict | (err <= 4e-7 * ref.abs().max())).all().item())
@@ -134,7 +144,7 @@ def main():
                 timed(nop, 1), timed(nop, 1)
             sys.stderr.write("[diag %s] rank %d rows %d | x-exch %.2f (recv %d send %d) | push %.2f (nnz %d, %d rows, hub "
                              "%d) | p-exch %.2f (recv %d) | pull %.2f (nnz %d) | add %.2f | early %.2f final %.2f\n" % (
-                                 spec, rank, hi - lo, t_x, sum(part.xrecv_splits), int(part.send_idx.numel()), t_push,
+                                 spec, rank, part.n_own, t_x, sum(part.xrecv_splits), int(part.send_idx.numel()), t_push,
                                  part.push.nnz, part.n_psend, part.n_psend_hub, t_p, part.n_precv, t_pull,
                                  part.pull.nnz, t_add, t_early, t_final))
             sys.stderr.flush()

@@ -77,6 +77,17 @@ def main():
         torch.cuda.synchronize()
         dist.barrier()
         del part
+    # ---- cyclic virtual-block layout (hub blocks spread over all ranks; renumbered vertex order) -----------------
+    vb = gdist.lshape_bounds(hist.cpu().numpy(), bin_size, n, world * 3, row_weight=6.0)
+    for name, kw in variants[:2]:
+        part = gdist.LShapedSpMM.from_full_cyclic(full, vb, rank, world, d, **kw)
+        sel = part.rows_old
+        assert sum(part.xrecv_splits) > 0 and part.xrecv_splits[rank] == 0
+        for step, x in enumerate(xs):
+            close(part.spmm(x[sel]), full.spmm(x)[sel], f"cyclic {name} step {step} rank {rank}")
+        torch.cuda.synchronize()
+        dist.barrier()
+        del part
     # ---- the transposed product (backward aggregation A_hat^T G): a second partition of the explicit transpose, with
     # bounds skewed by rank weights (what the measured rebalancing of bench.py produces) -------------------------
     full_t = full.transpose()

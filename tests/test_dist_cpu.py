@@ -121,7 +121,7 @@ def _skewed_matrix(n, seed):
     return a
 
 
-def _lshape_worker(rank, world, port, n, d, out):
+def _lshape_worker(rank, world, port, n, d, out, cyclic_m=0):
     os.environ["MASTER_ADDR"] = "127.0.0.1"
     os.environ["MASTER_PORT"] = str(port)
     dist.init_process_group("gloo", rank=rank, world_size=world)
@@ -133,18 +133,30 @@ def _lshape_worker(rank, world, port, n, d, out):
     coo = m.tocoo()
     hist, size = gdist.coarse_histogram(torch.from_numpy(coo.row.astype(np.int64)),
                                         torch.from_numpy(coo.col.astype(np.int64)), n, 64)
-    bounds = gdist.lshape_bounds(hist.numpy(), size, n, world, row_weight=2.0)
-    lo, hi = int(bounds[rank]), int(bounds[rank + 1])
-    blk = m[lo:hi]
-    local = DeviceCSR(torch.from_numpy(blk.indptr.astype(np.int32)), torch.from_numpy(blk.indices.astype(np.int32)),
-                      torch.from_numpy(blk.data), hi - lo, n)
-    part = gdist.LShapedSpMM(local, bounds, rank, world, d)
+    if cyclic_m:
+        # cyclic ownership of world * cyclic_m virtual blocks: the object works in a renumbered vertex order
+        vb = gdist.lshape_bounds(hist.numpy(), size, n, world * cyclic_m, row_weight=2.0)
+        full = DeviceCSR(torch.from_numpy(m.indptr.astype(np.int32)), torch.from_numpy(m.indices.astype(np.int32)),
+                         torch.from_numpy(m.data), n, n)
+        part = gdist.LShapedSpMM.from_full_cyclic(full, vb, rank, world, d)
+        rows_old = part.rows_old.numpy()
+        bounds = part.bounds
+        blk = m[rows_old]
+        x_mine = x[rows_old]
+    else:
+        bounds = gdist.lshape_bounds(hist.numpy(), size, n, world, row_weight=2.0)
+        lo, hi = int(bounds[rank]), int(bounds[rank + 1])
+        blk = m[lo:hi]
+        x_mine = x[lo:hi]
+        local = DeviceCSR(torch.from_numpy(blk.indptr.astype(np.int32)), torch.from_numpy(blk.indices.astype(np.int32)),
+                          torch.from_numpy(blk.data), hi - lo, n)
+        part = gdist.LShapedSpMM(local, bounds, rank, world, d)
 
     def to_sp(c):
         return sp.csr_matrix((c.val.numpy(), c.col.numpy(), c.rowptr.numpy()), shape=(c.n_rows, c.n_cols))
 
     # one step with the device kernels replaced by torch/scipy equivalents, same order as LShapedSpMM.spmm
-    part.x_own.copy_(torch.from_numpy(x[lo:hi]))
+    part.x_own.copy_(torch.from_numpy(x_mine))
     part.xsend.copy_(part.x_own[part.send_idx])                                    # = gdr_gather_rows_f32
     dist.all_to_all_single(part.x_recv, part.xsend, part.xrecv_splits, part.xsend_splits)
     if part.n_psend:
@@ -160,8 +172,10 @@ def _lshape_worker(rank, world, port, n, d, out):
     dist.all_reduce(nnz_all)
     # the pull part never references columns of higher ranks; the push part only own columns
     own_cols_only = part.push.nnz == 0 or int(part.push.col.max()) < part.n_own
-    no_recv_from_higher = all(c == 0 for c in part.xrecv_splits[rank:])
-    no_partials_from_lower = all(c == 0 for c in part.precv_splits[:rank + 1])
+    no_recv_from_higher = all(c == 0 for c in part.xrecv_splits[rank:]) or bool(cyclic_m)
+    no_partials_from_lower = all(c == 0 for c in part.precv_splits[:rank + 1]) or bool(cyclic_m)
+    if cyclic_m:   # both directions between every pair of ranks; nothing to or from itself
+        own_cols_only = own_cols_only and part.xrecv_splits[rank] == 0 and part.precv_splits[rank] == 0
     out.put((rank, bool(ok), int(nnz_all.item()) == m.nnz, bool(own_cols_only and no_recv_from_higher
                                                                   and no_partials_from_lower),
              part.recv_rows, part.pull.nnz + part.push.nnz, [int(b) for b in bounds]))
@@ -189,6 +203,43 @@ def test_lshaped_partition_gloo(world):
     assert bounds[0] == 0 and bounds[-1] == n and all(b1 >= b0 for b0, b1 in zip(bounds, bounds[1:]))
     loads = [r[5] for r in sorted(res)]
     assert max(loads) < 1.5 * sum(loads) / world, loads  # L-shapes, not row blocks, carry equal nnz
+
+
+@pytest.mark.parametrize("world,m", [(2, 3), (3, 2)])
+def test_lshaped_partition_cyclic_virtual_blocks_gloo(world, m):
+    """The cyclic virtual-block layout (hub blocks spread over all ranks): same product, every entry multiplied once."""
+    ctx = mp.get_context("spawn")
+    out = ctx.Queue()
+    port = _free_port()
+    n = 700
+    procs = [ctx.Process(target=_lshape_worker, args=(r, world, port, n, 8, out, m)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = [out.get(timeout=180) for _ in procs]
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    assert all(r[1] for r in res), res
+    assert all(r[2] for r in res), res
+    assert all(r[3] for r in res), res
+    bounds = res[0][6]
+    assert bounds[0] == 0 and bounds[-1] == n
+    recv = [r[4] for r in sorted(res)]
+    assert min(recv) > 0                                   # every rank receives rows (no rank is a pure sender)
+
+
+def test_cyclic_vblock_layout_is_a_permutation():
+    import gdr_b200  # noqa: F401
+    from gdr_b200 import dist as gdist
+    vb = np.array([0, 3, 3, 10, 14, 20, 21], dtype=np.int64)        # 6 virtual blocks (one empty), 3 ranks
+    order, new_vb, rb = gdist.cyclic_vblock_layout(vb, 3)
+    assert order.tolist() == [0, 3, 1, 4, 2, 5]
+    assert new_vb.tolist() == [0, 3, 7, 7, 13, 20, 21] and rb.tolist() == [0, 7, 13, 21]
+    perm, inv = gdist.cyclic_permutation(vb, order, torch.device("cpu"))
+    assert sorted(perm.tolist()) == list(range(21)) and torch.equal(perm[inv], torch.arange(21))
+    assert perm[:7].tolist() == [0, 1, 2, 10, 11, 12, 13]
+    with pytest.raises(ValueError):
+        gdist.cyclic_vblock_layout(vb[:-1], 3)
 
 
 def test_lshape_bounds_balances_l_shapes():
