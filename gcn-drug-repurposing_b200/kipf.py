@@ -156,8 +156,7 @@ class _GraphConvFunction(torch.autograd.Function):
             elif x_csr is not None:
                 pre = x_csr.spmm(wp)                                    # sparse X · W   (layers.py:175-176, sparse=True)
             else:
-                wt = _t_pad(wp)                                         # Wᵀ [outp, in4]
-                pre = _gemm_nt(xp, wt[:, :xp.shape[1]].contiguous() if wt.shape[1] != xp.shape[1] else wt)
+                pre = _gemm_nt(xp, _t_pad(wp))                          # X [n, in4] · (Wᵀ [outp, in4])ᵀ
             out = a.spmm(pre.contiguous(), e1=out, out=out) if out is not None else a.spmm(pre.contiguous())
         n, outp = out.shape
         bp = None
