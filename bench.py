@@ -281,6 +281,17 @@ class CpuReferenceGCN:
         return self.tr.step(batch, self.beta)[0]
 
 
+def msi_config(n, nnz, d, iters_per_epoch):
+    """The workload description both arms print (identical dicts: the driver compares them)."""
+    return {"workload": "msi_gcn: 2-layer GSS GCN hidden 256 on the MSI-shaped weighted graph (BASELINE configs[1]); "
+                        "step = 1 epoch = %d iterations of fwd+loss+bwd+Adam" % iters_per_epoch,
+            "nodes": int(n), "nnz_adj": int(nnz), "d": int(d), "batch": MSI_BATCH, "num_layers": MSI_LAYERS,
+            "iters_per_epoch": int(iters_per_epoch),
+            "l2": "GPU arm: explicit 256 MiB L2 flush between timed steps; CPU arm: the working set (features, "
+                  "activations, adjacency: > 150 MB) exceeds the host caches",
+            "graph": "MSI-synth (real blobs absent upstream: .MISSING_LARGE_BLOBS)"}
+
+
 # ------------------------------------------------------------------------------------------------------
 # our arm, workload msi_gcn
 # ------------------------------------------------------------------------------------------------------
@@ -380,16 +391,12 @@ def run_msi_gcn(args):
         "metric": "gcn_epochs_per_s", "value": 1000.0 / ms_per_step, "unit": "epochs/s", "n_gpus": 1,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms_per_step, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-        "config": {"workload": "msi_gcn: 2-layer GSS GCN hidden 256 on the MSI-shaped weighted graph "
-                               "(BASELINE configs[1]); step = 1 epoch = %d iterations of fwd+loss+bwd+Adam" % iters_per_epoch,
-                   "nodes": n, "nnz_adj": int(nnz), "d": d, "batch": MSI_BATCH, "num_layers": MSI_LAYERS,
-                   "iters_per_epoch": iters_per_epoch, "l2": "explicit 256 MiB flush between timed steps",
-                   "graph": "MSI-synth (real blobs absent upstream: .MISSING_LARGE_BLOBS)",
-                   "layer1_aggregations": ("hoisted: P1 = A_hat X and T1 = A_hat (P1*X) do not depend on the weights and are "
-                                           "reused while the resident feature tensor is unchanged (model.HOIST_LAYER1); the "
-                                           "e2e arm uploads a new feature tensor every iteration and recomputes them"
-                                           if hoisted else "recomputed every iteration"),
-                   "epochs_per_s_without_hoist": 1000.0 / ms_no_hoist, "ms_per_step_without_hoist": ms_no_hoist},
+        "config": msi_config(n, nnz, d, iters_per_epoch),
+        "layer1_hoist": {"layer1_aggregations": ("hoisted: P1 = A_hat X and T1 = A_hat (P1*X) do not depend on the weights "
+                                                 "and are reused while the resident feature tensor is unchanged "
+                                                 "(model.HOIST_LAYER1); the e2e arm uploads a new feature tensor every "
+                                                 "iteration and recomputes them" if hoisted else "recomputed every iteration"),
+                         "epochs_per_s_without_hoist": 1000.0 / ms_no_hoist, "ms_per_step_without_hoist": ms_no_hoist},
         "e2e": {"value": args.steps / e2e_s, "unit": "epochs/s", "h2d_bytes_per_step": h2d // args.steps,
                 "d2h_bytes_per_step": d2h // args.steps},
         "gpu_launches": int(launches),
@@ -1128,8 +1135,7 @@ def run_reference(args, workload):
         return {"impl": "reference", "metric": "gcn_epochs_per_s", "value": value, "unit": "epochs/s",
                 "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": s_per_iter * 1e3,
                 "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-                "config": {"workload": "msi_gcn (same inputs as the GPU arm)", "nodes": n, "nnz_adj": int(cpu.nnz),
-                           "d": MSI_D, "batch": MSI_BATCH, "iters_per_epoch": iters_per_epoch},
+                "config": msi_config(n, int(cpu.nnz), MSI_D, iters_per_epoch),
                 "cpu_baseline": {"value": value, "unit": "epochs/s", "cores": cores, "kind": "port", "sample": sample},
                 "e2e": {"value": value, "unit": "epochs/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
                 "gpu_launches": 0}
