@@ -9,6 +9,7 @@
 #include <stdlib.h>
 
 #include <algorithm>
+#include <atomic>
 
 #include "gemm_tc.cuh"
 
@@ -357,6 +358,111 @@ int gdr_adam_step_multi_f32(int n_tensors, float *const *params, const float *co
   adam_multi_kernel<<<(unsigned)ceil_div<int64_t>(total, 256), 256, 0, as_stream(stream)>>>(
       a, total, (float)(lr / bc1), (float)sqrt(bc2), (float)(1.0 - beta1), (float)beta2, (float)(1.0 - beta2),
       (float)eps);
+  GDR_LAUNCHED();
+  return GDR_OK;
+}
+
+}  // extern "C"
+
+// ---- GSS loss without any allocation: scratch lives inside the library ---------------------------------------
+// Who this is for: code that may not (or cannot) obtain device memory at call time.  Examples: a plug-in hosted by a
+// process whose memory pool is owned by somebody else and is not exposed to the plug-in, a real-time / serving loop
+// that forbids allocator calls after start-up because cudaMalloc takes a device-wide lock and may synchronise, and a
+// bare C or Fortran host that links libgdr.so but carries no allocator of its own.  Such a caller can still hand over
+// its inputs and outputs (it has those anyway); what it cannot supply is the B x d + B x B workspace that
+// gdr_gss_loss_fwd_bwd_f32 asks for.  Here that workspace is a fixed array in the library's own device image.
+//
+// Cost and limit: the array below is part of the module, so EVERY GPU on which this library's kernels get loaded keeps
+// GSS_STATIC_BYTES (about 18.1 MiB) reserved until the process exits, used or not.  It is sized for the training
+// batch of the reference (train.py --batch-size 2048, hidden 256): B <= 2048 and B*d <= 2048*256.  Anything larger
+// is refused with GDR_E_SHAPE; use the workspace form for it.
+constexpr int64_t GSS_STATIC_MAX_B = 2048;
+constexpr int64_t GSS_STATIC_MAX_BD = GSS_STATIC_MAX_B * 256;
+constexpr int64_t GSS_STATIC_E_BYTES = GSS_STATIC_MAX_BD * 4;                           // gathered rows E [B, d]
+constexpr int64_t GSS_STATIC_W_BYTES = GSS_STATIC_MAX_B * GSS_STATIC_MAX_B * 4;         // 2·dG [B, ldw]
+constexpr int64_t GSS_STATIC_P_BYTES = (GSS_STATIC_MAX_B / GBM) * (GSS_STATIC_MAX_B / GBM) * 8;  // one fp64 per CTA
+constexpr int64_t GSS_STATIC_BYTES = GSS_STATIC_E_BYTES + GSS_STATIC_W_BYTES + GSS_STATIC_P_BYTES;
+static_assert(GSS_STATIC_E_BYTES % 256 == 0 && GSS_STATIC_W_BYTES % 256 == 0, "sub-buffers stay 256-byte aligned");
+
+static __device__ __align__(256) unsigned char g_gss_static_scratch[GSS_STATIC_BYTES];
+
+// In host code `g_gss_static_scratch` is only a handle for the runtime, not an address a kernel can use: the device
+// address differs per GPU and has to be asked for with that GPU current.  One slot per device ordinal.
+constexpr int GSS_STATIC_MAX_DEVICES = 64;
+static std::atomic<unsigned char *> g_gss_static_ptr[GSS_STATIC_MAX_DEVICES];
+
+static int gss_static_scratch(unsigned char **out) {
+  int dev = -1;
+  GDR_CUDA(cudaGetDevice(&dev));
+  GDR_CHECK_ARG(dev >= 0 && dev < GSS_STATIC_MAX_DEVICES, GDR_E_INTERNAL,
+                "gss_loss_static: device ordinal %d outside the %d slots of the address table", dev,
+                GSS_STATIC_MAX_DEVICES);
+  unsigned char *p = g_gss_static_ptr[dev].load(std::memory_order_acquire);
+  if (p == nullptr) {  // first call on this device (two threads racing here both get the same answer)
+    void *sym = nullptr;
+    GDR_CUDA(cudaGetSymbolAddress(&sym, g_gss_static_scratch));
+    GDR_CHECK_ARG(sym != nullptr, GDR_E_INTERNAL, "gss_loss_static: cudaGetSymbolAddress returned a null address");
+    p = static_cast<unsigned char *>(sym);
+    g_gss_static_ptr[dev].store(p, std::memory_order_release);
+  }
+  *out = p;
+  return GDR_OK;
+}
+
+extern "C" {
+
+// Same result as gdr_gss_loss_fwd_bwd_f32 (same kernels, same order of operations), no workspace argument, and no
+// cudaMalloc / cudaFree / allocating library call anywhere below.
+//   - limits: 0 < B <= 2048, B*d <= 524288, d % 4 == 0; otherwise GDR_E_SHAPE and nothing is launched.
+//   - the first call on each device looks up the device address of the scratch array (cudaGetSymbolAddress, which may
+//     also make the runtime load this module on that device).  Make that first call during set-up, outside any
+//     stream capture, with the device you will run on current; later calls on that device only launch kernels.
+//   - all calls on one device share the one array.  Two calls that can overlap on the GPU (different streams without
+//     an event between them, or two host threads) overwrite each other's intermediate data: serialise them.
+//   - the array still holds whatever the previous call left there.  Nothing in it has to start at zero: every byte
+//     this call reads (E rows, the padded 2·dG rows, one loss partial per CTA) is written earlier in the same call.
+int gdr_gss_loss_fwd_bwd_static_f32(const float *embs, const int64_t *index, int64_t b, int64_t n, int64_t d,
+                                    float alpha, float beta, float *loss_out, float *grad_e_out,
+                                    gdr_stream_t stream) {
+  GDR_CHECK_ARG(b > 0 && n > 0 && d > 0, GDR_E_BADARG, "gss_loss_static: bad sizes");
+  GDR_CHECK_ARG(d % 4 == 0, GDR_E_SHAPE, "gss_loss_static: d must be a multiple of 4");
+  GDR_CHECK_ARG(b <= GSS_STATIC_MAX_B && b * d <= GSS_STATIC_MAX_BD, GDR_E_SHAPE,
+                "gss_loss_static: B=%lld, d=%lld exceeds the built-in scratch (B <= %lld and B*d <= %lld); use "
+                "gdr_gss_loss_fwd_bwd_f32 with a caller-owned workspace",
+                (long long)b, (long long)d, (long long)GSS_STATIC_MAX_B, (long long)GSS_STATIC_MAX_BD);
+  GDR_CHECK_ARG(embs && loss_out && grad_e_out, GDR_E_BADARG, "gss_loss_static: null pointer");
+  unsigned char *scratch = nullptr;
+  if (int rc = gss_static_scratch(&scratch)) return rc;
+  cudaStream_t st = as_stream(stream);
+  const int64_t ldw = align_up(b, 4);
+  const int64_t tiles = ceil_div<int64_t>(b, GBM);
+  float *e = reinterpret_cast<float *>(scratch);
+  float *wm = reinterpret_cast<float *>(scratch + GSS_STATIC_E_BYTES);
+  double *partials = reinterpret_cast<double *>(scratch + GSS_STATIC_E_BYTES + GSS_STATIC_W_BYTES);
+
+  gather_rows_kernel<<<(unsigned)ceil_div<int64_t>(b * 32, 256), 256, 0, st>>>(embs, index, b, n, d, e);
+  GDR_LAUNCHED();
+
+  GemmParams g{};  // G = E·Eᵀ; the epilogue leaves one loss partial per CTA and the 2·dG tile
+  g.a[0] = e; g.lda[0] = d; g.b[0] = e; g.ldb[0] = d; g.kseg[0] = d; g.nseg = 1;
+  g.m = b; g.n = b; g.c = wm; g.ldc = ldw;
+  g.alpha = alpha; g.beta = beta;
+  g.wscale = (float)(2.0 / ((double)b * (double)b));
+  g.loss_partials = partials;
+  dim3 grid((unsigned)tiles, (unsigned)tiles, 1);
+  gemm_f32_kernel<true, true, EPI_GSS><<<grid, GTHREADS, 0, st>>>(g);
+  GDR_LAUNCHED();
+
+  loss_finalize_kernel<<<1, 256, 0, st>>>(partials, (int)(tiles * tiles), 1.0 / ((double)b * (double)b), loss_out);
+  GDR_LAUNCHED();
+
+  GemmParams q{};  // dE = 2·dG · E
+  q.a[0] = wm; q.lda[0] = ldw;
+  q.b[0] = e; q.ldb[0] = d;
+  q.kseg[0] = b; q.nseg = 1;
+  q.m = b; q.n = d; q.c = grad_e_out; q.ldc = d;
+  dim3 grid2((unsigned)ceil_div<int64_t>(d, GBN), (unsigned)tiles, 1);
+  gemm_f32_kernel<true, false, EPI_STORE><<<grid2, GTHREADS, 0, st>>>(q);
   GDR_LAUNCHED();
   return GDR_OK;
 }

@@ -203,6 +203,24 @@ int gdr_gss_loss_fwd_bwd_f32(const float *embs, const int64_t *index, int64_t b,
                              int64_t n, int64_t d, float alpha, float beta,
                              float *loss_out, float *grad_e_out, void *workspace,
                              int64_t workspace_bytes, gdr_stream_t stream);
+/* The same loss and gradient for callers that cannot allocate device memory.  NO COUNTERPART IN THE REFERENCE
+ * (torch allocates freely there); it exists for hosts that cannot give this library a workspace: a plug-in inside a
+ * process whose device-memory pool belongs to someone else, a latency-critical loop where allocator calls
+ * (cudaMalloc takes a device-wide lock and may synchronise) are banned after start-up, or a plain C / Fortran
+ * program without a device allocator.  Inputs and outputs still come from the caller; the B x d + B x B workspace
+ * is a fixed 18.1 MiB array inside libgdr.so, held on every GPU that loads the library until the process exits.
+ *   - limits: B <= 2048 and B*d <= 2048*256 (the reference's training batch, train.py --batch-size 2048 at
+ *     hidden 256); larger sizes return GDR_E_SHAPE without launching anything.
+ *   - makes no cudaMalloc / cudaFree / allocating library call.
+ *   - the first call on each device resolves the array's device address (cudaGetSymbolAddress): do it once at
+ *     set-up, with that device current and before any stream capture begins.
+ *   - one array per GPU, shared by every call: calls that may overlap on the GPU (two streams, two threads) race
+ *     on it, so keep them ordered.  Stale contents from the previous call are harmless (each call writes every
+ *     byte it later reads).
+ * Results equal gdr_gss_loss_fwd_bwd_f32 on the same inputs.                                                  */
+int gdr_gss_loss_fwd_bwd_static_f32(const float *embs, const int64_t *index, int64_t b,
+                                    int64_t n, int64_t d, float alpha, float beta,
+                                    float *loss_out, float *grad_e_out, gdr_stream_t stream);
 /* dst[i,:] = src[index[i],:]  (embs[index], model.py:216; also the send-buffer pack of the partitioned SpMM) */
 int gdr_gather_rows_f32(const float *src, const int64_t *index, int64_t b, int64_t n, int64_t d,
                         float *dst, gdr_stream_t stream);
