@@ -29,11 +29,13 @@ from .graph import device_csr_of
 GEMM_BACKEND = os.environ.get("GDR_GEMM", "tc")
 
 # The first layer's two aggregations P¹ = Â·X and T¹ = Â·(P¹ ⊙ X) (modules/model.py:163,168-169) depend only on the
-# input features and the adjacency, not on the weights (SURVEY §3.1 "hoistable").  When the SAME feature tensor
-# object (unchanged: same _version) meets the same adjacency again they are reused instead of recomputed — the way
-# the CSR conversion of the adjacency is reused.  train.py:159 builds a new device tensor every iteration
-# (`features.cuda()`), which never hits; a resident-features loop (trainer.GCNTrainer) hits from the 2nd iteration on.
-# GDR_HOIST=0 disables it.
+# input features and the adjacency, not on the weights (SURVEY §3.1 "hoistable").  Reusing them is OPT-IN
+# (`model.hoist_layer1 = True`; trainer.GCNTrainer does it for the resident feature matrix it owns): the owner of the
+# features is the only one who can promise that nobody rewrites them behind torch's back.  The cache belongs to the
+# model object (dropped with it) and is keyed on the feature tensor object, its `_version`, its shape and the
+# adjacency's CSR object.  `_version` sees torch's in-place ops but NOT writes through `.data`, through raw pointers
+# (libgdr's `out=` arguments) or edits of the CSR values: after any of those call `model.invalidate_layer1_cache()`.
+# GDR_HOIST=0 switches the reuse off everywhere, whatever the models ask for.
 HOIST_LAYER1 = os.environ.get("GDR_HOIST", "1") != "0"
 
 
@@ -68,28 +70,51 @@ def _check_layer_shapes(x, w1, b1, w2, b2, csr):
             raise RuntimeError(f"{nm} must be an fp32 CUDA tensor (call model.cuda(); there is no CPU path)")
 
 
-def _aggregate(csr, x, hoist_key=None):
-    """P = Â·x and T = Â·(P ⊙ x).  hoist_key: the caller's feature tensor OBJECT when these are the first layer's
-    aggregations; a strong reference is kept so that its storage cannot be recycled under the same address."""
-    if hoist_key is not None and HOIST_LAYER1:
-        c = getattr(csr, "_layer1_cache", None)
-        if (c is not None and c[0]._cdata == hoist_key._cdata and c[1] == hoist_key._version
-                and c[2] == tuple(x.shape)):      # same TensorImpl (kept alive by c[0]), never written since
-            return c[3], c[4]
+class Layer1Cache:
+    """P¹, T¹ of one (feature tensor, adjacency) pair.  Holds a strong reference to the feature tensor so that its
+    storage cannot be recycled under the same address while the entry lives."""
+
+    def __init__(self):
+        self.entry = None
+        self.hits = 0
+
+    def clear(self):
+        self.entry = None
+
+    def lookup(self, csr, key, x):
+        c = self.entry
+        if (c is not None and c[0] is csr and c[1]._cdata == key._cdata and c[2] == key._version
+                and c[3] == tuple(x.shape)):      # same CSR, same TensorImpl, no torch-visible write since
+            self.hits += 1
+            return c[4], c[5]
+        return None
+
+    def store(self, csr, key, x, p, t):
+        self.entry = (csr, key, key._version, tuple(x.shape), p, t)
+
+
+def _aggregate(csr, x, hoist_key=None, cache=None):
+    """P = Â·x and T = Â·(P ⊙ x).  hoist_key + cache: the caller's feature tensor OBJECT and the owning model's
+    Layer1Cache when these are the first layer's aggregations and the model has opted in."""
+    use = hoist_key is not None and cache is not None and HOIST_LAYER1
+    if use:
+        hit = cache.lookup(csr, hoist_key, x)
+        if hit is not None:
+            return hit
     p, px = csr.spmm(x, out2_mul=x)      # model.py:163, and torch.mul(P, X) of :168 from the same launch
     t = csr.spmm(px)                     # model.py:169
-    if hoist_key is not None and HOIST_LAYER1:
-        csr._layer1_cache = (hoist_key, hoist_key._version, tuple(x.shape), p, t)
+    if use:
+        cache.store(csr, hoist_key, x, p, t)
     return p, t
 
 
-def layer_forward_raw(csr, x, w1, b1, w2, b2, residual, decay, hoist_key=None):
+def layer_forward_raw(csr, x, w1, b1, w2, b2, residual, decay, hoist_key=None, cache=None):
     """One GSS_GNNLayer application (+ the residual update of the network loop).
     Returns P = Â·x, T = Â·(P⊙x), Z (pre-nonlinearity), Xnext (= ELU(Z) or residual + decay*ELU(Z))."""
     L = _ffi.lib()
     _check_layer_shapes(x, w1, b1, w2, b2, csr)
     n, d = x.shape
-    p, t = _aggregate(csr, x, hoist_key)
+    p, t = _aggregate(csr, x, hoist_key, cache)
     z = torch.empty_like(x)
     xnext = torch.empty_like(x)
     if GEMM_BACKEND == "tc":
@@ -191,7 +216,7 @@ class _ResGCNFunction(torch.autograd.Function):
     """hidden_emb = normalize(X^{L+1}) for the whole residual network (weights shared across depth)."""
 
     @staticmethod
-    def forward(ctx, x_in, w1, b1, w2, b2, csr, num_layers, decay):
+    def forward(ctx, x_in, w1, b1, w2, b2, csr, num_layers, decay, cache=None):
         L = _ffi.lib()
         x = _check_dense(x_in, "x")
         w1c, b1c, w2c, b2c = w1.contiguous(), b1.contiguous(), w2.contiguous(), b2.contiguous()
@@ -200,9 +225,11 @@ class _ResGCNFunction(torch.autograd.Function):
         residual = None
         cur = x
         for li in range(num_layers):
-            # layer 1 aggregates the caller's features: reusable while that tensor object is unchanged
-            key = x_in if (li == 0 and x is x_in and not x_in.requires_grad) else None
-            p, t, z, xnext = layer_forward_raw(csr, cur, w1c, b1c, w2c, b2c, residual, decay, hoist_key=key)
+            # layer 1 aggregates the caller's features: reusable (when the model opted in: cache is not None) while
+            # that tensor object is unchanged
+            key = x_in if (li == 0 and cache is not None and x is x_in and not x_in.requires_grad) else None
+            p, t, z, xnext = layer_forward_raw(csr, cur, w1c, b1c, w2c, b2c, residual, decay, hoist_key=key,
+                                               cache=cache)
             xs.append(cur), ps.append(p), ts.append(t), zs.append(z)
             residual = z
             cur = xnext
@@ -251,7 +278,7 @@ class _ResGCNFunction(torch.autograd.Function):
             gx = layer_backward_raw(csr_t, gz, xs[i - 1], ps[i - 1], ts[i - 1], w1c, w2c, (dw1, db1, dw2, db2),
                                     accumulate=(i != nl), need_gx=need_gx, ws=ws)
             gxnext = gx
-        return (gx if ctx.need_gx else None), dw1, db1, dw2, db2, None, None, None
+        return (gx if ctx.need_gx else None), dw1, db1, dw2, db2, None, None, None, None
 
 
 class _GSSLossFunction(torch.autograd.Function):
@@ -334,6 +361,14 @@ class ResidualGraphConvolutionalNetwork(nn.Module):
         self.init_weights = init_weights
         self.layer_decay = layer_decay
         self.gcn_layer = GSS_GNNLayer(hidden_units, init_weights)
+        # not in the reference: opt-in reuse of the first layer's aggregations (see HOIST_LAYER1 above)
+        self.hoist_layer1 = False
+        self._layer1_cache = Layer1Cache()
+
+    def invalidate_layer1_cache(self):
+        """Forget the cached P¹/T¹.  Needed after writing the features through `.data` / a raw pointer, or after
+        editing the adjacency values in place: torch's version counter does not see those."""
+        self._layer1_cache.clear()
 
     def decoder(self, x):
         """Unused by train.py (model.py:190-195); kept for API completeness, composed from this
@@ -349,7 +384,8 @@ class ResidualGraphConvolutionalNetwork(nn.Module):
         csr = device_csr_of(adj)
         g = self.gcn_layer
         return _ResGCNFunction.apply(x, g.dense.weight, g.dense.bias, g.dense2.weight, g.dense2.bias, csr,
-                                     int(self.num_layers), float(self.layer_decay))
+                                     int(self.num_layers), float(self.layer_decay),
+                                     self._layer1_cache if self.hoist_layer1 else None)
 
 
 class _NormalizeFunction(torch.autograd.Function):

@@ -64,7 +64,7 @@ class GCNTrainer:
     """Model + optimizer + loss of train.py:111-150, features and adjacency resident on the device."""
 
     def __init__(self, features, adj, hidden_units, num_layers=2, layer_decay=0.3, init_weights=1e-5, alpha=1.0,
-                 lr=1e-4, batch_size=2048, beta=None, beta_percentile=None, device="cuda"):
+                 lr=1e-4, batch_size=2048, beta=None, beta_percentile=None, device="cuda", hoist_layer1=True):
         self.device = torch.device(device)
         self.dataset = DiffusionDataSet(features=features, adj=adj.to(self.device))
         n = len(self.dataset)
@@ -81,6 +81,15 @@ class GCNTrainer:
         self.beta_percentile = beta_percentile
         self.features_dev = self.dataset.features.to(self.device)
         self.hidden_emb = None
+        # The trainer owns `features_dev` and never writes it, so it may let the model reuse the first layer's
+        # aggregations across iterations (model.HOIST_LAYER1).  Only for that resident tensor: features passed to
+        # iteration() explicitly are somebody else's and are always aggregated afresh.
+        self.hoist_layer1 = bool(hoist_layer1)
+
+    def invalidate(self):
+        """Call after changing `features_dev` or the adjacency values in place by means torch cannot see (`.data`,
+        libgdr `out=` writes): drops the cached first-layer aggregations."""
+        self.model.invalidate_layer1_cache()
 
     def loader(self, shuffle=True):
         return DiffusionDataLoader(self.dataset, batch_size=self.batch_size, num_workers=6, shuffle=shuffle)
@@ -96,6 +105,7 @@ class GCNTrainer:
     def iteration(self, batch, features=None):
         """train.py:157-184.  batch: int64 index tensor on the device."""
         x = self.features_dev if features is None else features
+        self.model.hoist_layer1 = self.hoist_layer1 and features is None
         hidden_emb = self.model(x=x, adj=self.dataset.adj)
         if self.beta is None:
             self.beta = self.select_beta(hidden_emb)
