@@ -78,12 +78,18 @@ class _WalkerBase:
         L = _ffi.lib()
         order = list(range(g.n))
         walks = torch.empty(num_walks * g.n, walk_length, dtype=torch.int32, device=g.rowptr.device)
+        # walker.py:47,102: a new node order every pass.  The reference's node2vec walker takes nothing else from
+        # Python's `random` (alias_draw uses np.random), so all shuffles are drawn first, back to back, and only then
+        # the seed of the device stream: after random.seed(s) every pass starts in the reference's order.
+        orders = []
+        for _ in range(num_walks):
+            random.shuffle(order)
+            orders.append(list(order))
         seed = random.getrandbits(63)
         print('Walk iteration:')
         for it in range(num_walks):
             print(str(it + 1), '/', str(num_walks))
-            random.shuffle(order)                                   # walker.py:47,102: a new node order every pass
-            start = torch.tensor(order, dtype=torch.int32, device=walks.device)
+            start = torch.tensor(orders[it], dtype=torch.int32, device=walks.device)
             _ffi.check(L.gdr_node2vec_walks(_ffi.ptr(g.rowptr), _ffi.ptr(g.col), _ffi.ptr(g.cum), g.n, _ffi.ptr(start),
                                             g.n, walk_length, float(getattr(self, "p", 1.0)), float(getattr(self, "q", 1.0)),
                                             1 if self.second_order else 0, seed, it * g.n,
