@@ -18,6 +18,13 @@
 //      is not certified (near-ties inside the margin deeper than the list) is recomputed by the exact fp64 kernel
 //      (gram_topk_f64_rows_kernel).  The index sets therefore equal those of gdr_gram_topk_f64 bit for bit, genuine
 //      fp64 ties excepted, whatever the data; the margin only decides how many rows take the slow path.
+//      Range: the bound above is a RELATIVE one and holds only while every operand and product is a normal fp32
+//      number.  Step 0 therefore multiplies X by 2^-e, e = exponent of max |x_ik| (exact, and a common positive
+//      factor changes no ranking), so that the largest entry lies in [1, 2): nothing can overflow fp32, and whatever
+//      still falls below the fp32 normal range (entries or products under 2^-126 relative to the largest entry) costs
+//      at most 2^-126 of absolute error per term.  The margin carries that as an absolute addend d * 2^-120; rows
+//      whose scale is so small that the addend matters are simply not certified and take the fp64 path.  (|e| is
+//      clamped to 500; data whose Gram entries overflow fp64 itself is outside any guarantee, here and upstream.)
 //
 // Kernel structure (persistent, one CTA per SM, warp-specialised; operand A never is a shared-memory operand):
 //   a work item = (128-row block, range of 128-column tiles).  The row block's operand (128 x d TF32, d <= 256) is
@@ -73,18 +80,46 @@ __device__ __forceinline__ void gt_trace(const GtParams &p, int role, uint32_t i
     p.trace[(role * 128 + (int)(idx - skip)) * 4 + ev] = clock64();
 }
 
-// ---- step 0: Xh = rn_tf32(X) as fp32 [n, ldp] (zero padded), |x_i| rounded up, max_i |x_i| --------------------------
+// ---- step 0a: max |x_ik| over the whole matrix (bit pattern of a non-negative double orders like an integer) --------
+__global__ void __launch_bounds__(256)
+gram_absmax_kernel(const double *__restrict__ x, int64_t count, unsigned long long *__restrict__ absmax_bits) {
+  unsigned long long m = 0ull;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < count; i += (int64_t)gridDim.x * blockDim.x) {
+    const unsigned long long b = (unsigned long long)__double_as_longlong(fabs(__ldg(x + i)));
+    m = b > m ? b : m;
+  }
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    const unsigned long long other = __shfl_xor_sync(0xffffffffu, m, o);
+    m = other > m ? other : m;
+  }
+  if ((threadIdx.x & 31) == 0 && m != 0ull) atomicMax(absmax_bits, m);
+}
+
+// exponent e with max |x| in [2^e, 2^(e+1)), clamped; 0 for an all-zero (or non-finite) matrix
+__device__ __forceinline__ int gt_scale_exponent(unsigned long long absmax_bits) {
+  const double m = __longlong_as_double((long long)absmax_bits);
+  if (!(m > 0.0) || isinf(m)) return 0;
+  const int e = ilogb(m);
+  return e < -500 ? -500 : (e > 500 ? 500 : e);
+}
+
+// ---- step 0b: Xh = rn_tf32(X * 2^-e) as fp32 [n, ldp] (zero padded), |x_i| 2^-e rounded up, max_i of it --------------
 __global__ void __launch_bounds__(256)
 gram_prep_kernel(const double *__restrict__ x, int64_t n, int64_t d, int64_t ldp, float *__restrict__ xh,
-                 float *__restrict__ norms, unsigned int *__restrict__ maxnorm_bits) {
+                 float *__restrict__ norms, unsigned int *__restrict__ maxnorm_bits,
+                 const unsigned long long *__restrict__ absmax_bits, int *__restrict__ exp_out) {
   const int lane = threadIdx.x & 31;
   const int64_t row = (int64_t)blockIdx.x * 8 + (threadIdx.x >> 5);
+  const int e = gt_scale_exponent(*absmax_bits);
+  if (blockIdx.x == 0 && threadIdx.x == 0) *exp_out = e;
   if (row >= n) return;
+  const double scale = ldexp(1.0, -e);
   double s = 0.0;
   for (int64_t c = lane; c < ldp; c += 32) {
     float h = 0.f;
     if (c < d) {
-      const double v = __ldg(x + row * d + c);
+      const double v = __ldg(x + row * d + c) * scale;   // exact: a power of two
       s = fma(v, v, s);
       h = __uint_as_float(tc::cvt_tf32((float)v));
     }
@@ -382,7 +417,7 @@ __global__ void __launch_bounds__(32 * RR_WARPS)
 gram_topk_rerank_kernel(const double *__restrict__ x, int64_t n, int64_t d, int k, int lists, int c,
                         const int32_t *__restrict__ cand_idx, const float *__restrict__ cand_thr,
                         const float *__restrict__ norms, const unsigned int *__restrict__ maxnorm_bits,
-                        int32_t *__restrict__ idx_out, double *__restrict__ val_out, int32_t *__restrict__ fail_count,
+                        const int *__restrict__ scale_exp, int32_t *__restrict__ idx_out, double *__restrict__ val_out, int32_t *__restrict__ fail_count,
                         int32_t *__restrict__ fail_rows) {
   extern __shared__ __align__(16) unsigned char rr_smem[];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -440,8 +475,11 @@ gram_topk_rerank_kernel(const double *__restrict__ x, int64_t n, int64_t d, int 
   if (lane == 0) {
     float theta = -INFINITY;
     for (int l = 0; l < lists; ++l) theta = fmaxf(theta, cand_thr[row * lists + l]);
-    const double margin = GT_DELTA * (double)norms[row] * (double)__uint_as_float(*maxnorm_bits);
-    const bool certified = (theta == -INFINITY) || ((double)theta + margin < vk);
+    // theta, the norms and the margin live in the scaled domain (X * 2^-e); vk is exact and unscaled
+    const double vk_scaled = vk * ldexp(1.0, -2 * *scale_exp);
+    const double margin = GT_DELTA * (double)norms[row] * (double)__uint_as_float(*maxnorm_bits) +
+                          (double)d * 7.52316384526264e-37;  // d * 2^-120: terms below the fp32 normal range
+    const bool certified = (theta == -INFINITY) || ((double)theta + margin < vk_scaled);
     if (!certified) fail_rows[atomicAdd(fail_count, 1)] = (int32_t)row;
   }
 }
@@ -616,10 +654,16 @@ int gdr_gram_topk_tc_f64(const double *x, int64_t n, int64_t d, int64_t k, int32
   int32_t *fail_rows = cv.take<int32_t>(n);
   int32_t *cand_idx = cv.take<int32_t>(n * lists * c);
   float *cand_thr = cv.take<float>(n * lists);
-  unsigned int *scal = cv.take<unsigned int>(64);  // [0] max norm bits, [1] fail count
-  GDR_CUDA(cudaMemsetAsync(scal, 0, 256, st));
+  unsigned int *scal = cv.take<unsigned int>(64);  // [0] max norm bits, [1] fail count, [2] scale exponent e,
+  GDR_CUDA(cudaMemsetAsync(scal, 0, 256, st));     // [4..5] max |x| bits (fp64)
+  unsigned long long *absmax_bits = reinterpret_cast<unsigned long long *>(scal + 4);
+  int *scale_exp = reinterpret_cast<int *>(scal + 2);
 
-  gram_prep_kernel<<<(unsigned)ceil_div<int64_t>(n, 8), 256, 0, st>>>(x, n, d, ldp, xh, norms, scal);
+  gram_absmax_kernel<<<(unsigned)std::min<int64_t>(ceil_div<int64_t>(n * d, 256 * 8), 8 * kNumSMs), 256, 0, st>>>(
+      x, n * d, absmax_bits);
+  GDR_LAUNCHED();
+  gram_prep_kernel<<<(unsigned)ceil_div<int64_t>(n, 8), 256, 0, st>>>(x, n, d, ldp, xh, norms, scal, absmax_bits,
+                                                                     scale_exp);
   GDR_LAUNCHED();
 
   CUtensorMap map;
@@ -640,7 +684,7 @@ int gdr_gram_topk_tc_f64(const double *x, int64_t n, int64_t d, int64_t k, int32
   const int rr_smem = (int)(RR_WARPS * (d * 8 + lists * c * 12));
   GDR_CUDA(cudaFuncSetAttribute(gram_topk_rerank_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, rr_smem));
   gram_topk_rerank_kernel<<<(unsigned)ceil_div<int64_t>(n, RR_WARPS), 32 * RR_WARPS, rr_smem, st>>>(
-      x, n, d, (int)k, lists, c, cand_idx, cand_thr, norms, scal, idx_out, val_out, fail_count, fail_rows);
+      x, n, d, (int)k, lists, c, cand_idx, cand_thr, norms, scal, scale_exp, idx_out, val_out, fail_count, fail_rows);
   GDR_LAUNCHED();
 
   // every CTA beyond the (device-side) number of failed rows exits at once: no host synchronisation

@@ -76,6 +76,29 @@ def test_gram_topk_tc_duplicate_rows_and_zero_rows(gdr):
     assert all(len(set(r)) == 5 for r in i_tc.tolist())
 
 
+@pytest.mark.parametrize("factor", [1e-25, 1e25, 2.0 ** -300, 2.0 ** 300])
+def test_gram_topk_tc_extreme_scales(gdr, factor):
+    """Entries far outside the fp32 range (1e25^2 overflows fp32, 1e-25^2 underflows it): the kernel rescales by a
+    power of two before the TF32 product, so the index sets still equal the fp64 kernel's and rows stay certified."""
+    x = np.random.default_rng(11).standard_normal((1500, 96)) * factor
+    i_tc, v_tc, i_64, v_64, nfb = _both(gdr, x, 5)
+    assert np.isfinite(v_tc).all()
+    assert np.array_equal(v_tc, v_64)
+    assert np.array_equal(np.sort(i_tc, axis=1), np.sort(i_64, axis=1))
+    assert nfb < 150, f"{nfb} rows fell back: the rescaling is not effective"
+
+
+def test_gram_topk_tc_rows_of_wildly_different_scale(gdr):
+    """Some rows 1e-30 times smaller than the rest: their TF32 operands fall below the fp32 normal range, the
+    relative error bound no longer covers them, and the absolute term of the margin sends them to the fp64 path."""
+    x = np.random.default_rng(12).standard_normal((1200, 64))
+    x[::7] *= 1e-42
+    i_tc, v_tc, i_64, v_64, nfb = _both(gdr, x, 5)
+    assert np.array_equal(v_tc, v_64)
+    s = x @ x.T
+    np.testing.assert_allclose(np.take_along_axis(s, i_tc.astype(np.int64), 1), v_tc, rtol=1e-12, atol=0)
+
+
 def test_gram_topk_tc_msi_scale(gdr):
     """N = 29,960, d = 128, k = 5 (SURVEY 8 'MSI-kNN'): full equality with the exact kernel."""
     n, d, k = 29960, 128, 5
@@ -84,7 +107,12 @@ def test_gram_topk_tc_msi_scale(gdr):
     assert np.array_equal(v_tc, v_64)
     same = (i_tc == i_64).all(axis=1)
     assert same.mean() > 0.9999       # exact fp64 ties may order differently
-    assert np.array_equal(np.sort(i_tc, axis=1)[same], np.sort(i_64, axis=1)[same])
+    # the rows that differ: every index either kernel returned must really carry the value returned with it (so the
+    # two answers differ only by a permutation inside, or a swap at the boundary of, a genuine fp64 tie)
+    for r in np.flatnonzero(~same):
+        for idx, val in ((i_tc[r], v_tc[r]), (i_64[r], v_64[r])):
+            assert len(set(idx.tolist())) == k
+            np.testing.assert_allclose(x[idx.astype(np.int64)] @ x[r], val, rtol=1e-12, atol=0)
     print(f"msi-scale gram top-k: {nfb} of {n} rows took the fp64 path")
     assert nfb < n // 100
 
