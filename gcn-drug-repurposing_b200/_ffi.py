@@ -52,7 +52,6 @@ _SIGNATURES = {
                                          c_i64, c_ptr]),
     "gdr_gss_loss_fwd_bwd_static_f32": (c_i32, [c_ptr, c_ptr, c_i64, c_i64, c_i64, c_f32, c_f32, c_ptr, c_ptr, c_ptr]),
     "gdr_gemm_nt_tc_workspace_bytes": (c_i64, [c_i64, c_i64, c_i64]),
-    "gdr_debug_tc_trace": (c_i32, [c_ptr]),
     "gdr_gemm_nt_tc_f32": (c_i32, [c_ptr, c_i64, c_ptr, c_i64, c_i64, c_i64, c_i64, c_ptr, c_i64, c_ptr, c_i64, c_ptr]),
     "gdr_gcn_layer_fwd_tc_workspace_bytes": (c_i64, [c_i64, c_i64]),
     "gdr_gcn_layer_fwd_tc_f32": (c_i32, [c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_ptr, c_f32, c_i64, c_i64, c_ptr,

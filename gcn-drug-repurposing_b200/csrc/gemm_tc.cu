@@ -17,6 +17,7 @@
 // the layer forward with the weight split, 105.5 us before the A-in-TMEM / 8-warp epilogue change.
 // Accuracy (tests/test_gpu_tc.py): max error 3-8e-7 of sum|a||b| (torch-CPU fp32: 2-5e-7).
 #include <algorithm>
+#include <atomic>
 
 #include "gemm_tc.cuh"
 #include "tc_ptx.cuh"
@@ -50,6 +51,7 @@ __device__ __forceinline__ void tc_trace(const TcParams &p, int role, uint32_t i
   if (p.trace != nullptr && blockIdx.x == 0 && idx < 128u) p.trace[(role * 128 + (int)idx) * 4 + ev] = clock64();
 }
 static long long *g_tc_trace = nullptr;
+constexpr int TC_MAX_DEVICES = 64;  // slots of the per-device "attribute already set" flags (beyond: set every call)
 long long *tc_trace_buffer() { return g_tc_trace; }
 
 // ---- operand split ---------------------------------------------------------------------------------
@@ -898,10 +900,12 @@ int tc_gemm_tn_splitk(const float *a, int64_t lda, int64_t m, const float *b1, i
   p.m = m; p.n = n1 + n2; p.k = k; p.k_per_split = k_per_split; p.splits = splits; p.k_a2 = n1;
   p.g.c = part; p.g.ldc = n1 + n2; p.colsum_part = colsum_part; p.trace = nullptr;
   constexpr int smem_bytes = tc_smem_bytes(true);
-  static bool attr_set = false;
-  if (!attr_set) {
+  static std::atomic<bool> attr_set[TC_MAX_DEVICES];  // the attribute is per device, not per process
+  int dev = 0;
+  GDR_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= TC_MAX_DEVICES || !attr_set[dev].load(std::memory_order_acquire)) {
     GDR_CUDA(cudaFuncSetAttribute(gemm_tc_tn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, smem_bytes));
-    attr_set = true;
+    if (dev >= 0 && dev < TC_MAX_DEVICES) attr_set[dev].store(true, std::memory_order_release);
   }
   const int64_t tiles = ceil_div<int64_t>(p.n, TC_BN) * ceil_div<int64_t>(m, TC_BM) * splits;
   const unsigned grid = (unsigned)std::min<int64_t>(tiles, kNumSMs);
@@ -940,11 +944,13 @@ static int launch_gemm_tc(const float *ahi, const float *alo, const float *bhi, 
   p.m = m; p.n = n; p.k = k; p.k_per_split = k_per_split; p.splits = splits > 0 ? splits : 1;
   p.k_a2 = RAW_A ? k_a2 : k; p.g = g; p.trace = g_tc_trace;
   constexpr int smem_bytes = tc_smem_bytes(EPI != EPI_HIST && EPI != EPI_MINGT);
-  static bool attr_set = false;  // per template instance
-  if (!attr_set) {
+  static std::atomic<bool> attr_set[TC_MAX_DEVICES];  // per template instance AND per device (the attribute is)
+  int dev = 0;
+  GDR_CUDA(cudaGetDevice(&dev));
+  if (dev < 0 || dev >= TC_MAX_DEVICES || !attr_set[dev].load(std::memory_order_acquire)) {
     GDR_CUDA(cudaFuncSetAttribute(gemm_tc_kernel<EPI, RAW_A>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                   smem_bytes));
-    attr_set = true;
+    if (dev >= 0 && dev < TC_MAX_DEVICES) attr_set[dev].store(true, std::memory_order_release);
   }
   const int64_t tiles = ceil_div<int64_t>(n, TC_BN) * ceil_div<int64_t>(m, TC_BM) * p.splits;
   const unsigned grid = (unsigned)std::min<int64_t>(tiles, kNumSMs);  // persistent: one CTA per SM walks the tiles
@@ -1018,8 +1024,10 @@ using namespace gdr;
 
 extern "C" {
 
-// Diagnostic hook: while `buf` (device, 4*128*4 int64, zeroed by the caller) is set, CTA 0 of every tensor-core GEMM
-// launch records clock64() at its pipeline hand-offs into it; nullptr switches the recording off.
+// Diagnostic hook, deliberately NOT part of include/gdr.h (process-global state has no place in the product ABI;
+// profiles/tc_pipeline_trace.py binds it by name): while `buf` (device, 4*128*4 int64, zeroed by the caller) is set,
+// CTA 0 of every tensor-core GEMM launch records clock64() at its pipeline hand-offs into it — buf[role][index][event],
+// roles 0 TMA producer, 1 MMA issuer, 2 converter warp, 3 epilogue warp; nullptr switches the recording off.
 int gdr_debug_tc_trace(long long *buf) {
   g_tc_trace = buf;
   return GDR_OK;

@@ -262,13 +262,19 @@ __global__ void loss_accumulate_kernel(const double *__restrict__ partials, int6
   }
 }
 
-int64_t gdr_gss_loss_tc_workspace_bytes(int64_t b, int64_t d) {
-  if (b < 0 || d <= 0) return GDR_E_BADARG;
+// workspace for a given panel height: the GDR_GSS_PANEL_ROWS override is read ONCE per entry-point call (by
+// gss_panel_rows) and everything else derives from that value, so the size check of the run function and its carving
+// cannot disagree even if the environment changes between the size query and the run.
+static int64_t gss_tc_workspace_for(int64_t b, int64_t d, int64_t r) {
   const int64_t ldw = align_up(b, 4);
-  const int64_t r = gss_panel_rows(b);
   const int64_t tiles_b = ceil_div<int64_t>(b > 0 ? b : 1, 128), tiles_r = ceil_div<int64_t>(r > 0 ? r : 1, 128);
   return 3 * align_up(b * d * 4, 256) + align_up(r * ldw * 4, 256) + 2 * align_up(d * ldw * 4, 256) +
          align_up(tiles_r * tiles_b * 8, 256) + align_up(gss_part_floats(r, d) * 4, 256) + 2048;
+}
+
+int64_t gdr_gss_loss_tc_workspace_bytes(int64_t b, int64_t d) {
+  if (b < 0 || d <= 0) return GDR_E_BADARG;
+  return gss_tc_workspace_for(b, d, gss_panel_rows(b));
 }
 
 int gdr_gss_loss_fwd_bwd_tc_f32(const float *embs, const int64_t *index, int64_t b, int64_t n, int64_t d, float alpha,
@@ -277,11 +283,11 @@ int gdr_gss_loss_fwd_bwd_tc_f32(const float *embs, const int64_t *index, int64_t
   GDR_CHECK_ARG(b > 0 && n > 0 && d > 0, GDR_E_BADARG, "gss_loss_tc: bad sizes");
   GDR_CHECK_ARG(d % 4 == 0, GDR_E_SHAPE, "gss_loss_tc: d must be a multiple of 4");
   GDR_CHECK_ARG(embs && loss_out && grad_e_out && workspace, GDR_E_BADARG, "gss_loss_tc: null pointer");
-  GDR_CHECK_ARG(workspace_bytes >= gdr_gss_loss_tc_workspace_bytes(b, d), GDR_E_WORKSPACE,
+  const int64_t rows = gss_panel_rows(b);
+  GDR_CHECK_ARG(workspace_bytes >= gss_tc_workspace_for(b, d, rows), GDR_E_WORKSPACE,
                 "gss_loss_tc: workspace too small");
   cudaStream_t st = as_stream(stream);
   const int64_t ldw = align_up(b, 4);
-  const int64_t rows = gss_panel_rows(b);
   const int64_t tiles_b = ceil_div<int64_t>(b, 128);
   Carver cv(workspace);
   float *e = cv.take<float>(b * d), *ehi = cv.take<float>(b * d), *elo = cv.take<float>(b * d);

@@ -158,10 +158,6 @@ int gdr_linear_bwd_weight_f32(const float *g, const float *a, int64_t n, int64_t
  * fp32 RN in the epilogue; TMA-fed, csrc/gemm_tc.cu).  Same arguments and results (to fp32 rounding
  * noise) as the functions above, plus a caller-owned workspace for the split operands.               */
 int64_t gdr_gemm_nt_tc_workspace_bytes(int64_t m, int64_t n, int64_t k);
-/* Diagnostic (no reference counterpart): while buf != NULL (device, 4*128*4 int64, zeroed by the caller) CTA 0 of
- * every tensor-core GEMM launch records clock64() at its pipeline hand-offs: buf[role][index][event], roles
- * 0 TMA producer, 1 MMA issuer, 2 converter warp, 3 epilogue warp (profiles/tc_pipeline_trace.py reads it).       */
-int gdr_debug_tc_trace(long long *buf);
 /* C[m,n] = A[m,k]·B[n,k]ᵀ, row-major, K contiguous: torch.mm(A, B.T) / np.dot(H, H.T) (train.py:166) */
 int gdr_gemm_nt_tc_f32(const float *a, int64_t lda, const float *b, int64_t ldb, int64_t m, int64_t n,
                        int64_t k, float *c, int64_t ldc, void *workspace, int64_t workspace_bytes,

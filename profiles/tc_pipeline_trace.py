@@ -6,6 +6,7 @@ Times the layer-forward GEMM (EPI_LAYER, A = [P | T] raw) and the plain NT GEMM 
 CUDA events, then records one launch of each with CTA 0's clock64() stamps at every hand-off of the producer /
 converter / MMA / epilogue roles and prints the per-k-block intervals.  Needs a B200; writes JSON next to the log.
 """
+import ctypes
 import json
 import sys
 
@@ -38,6 +39,7 @@ def time_it(fn, reps=20):
 
 def trace(fn):
     buf = torch.zeros(4 * 128 * 4, dtype=torch.int64, device=DEV)
+    L.gdr_debug_tc_trace.argtypes, L.gdr_debug_tc_trace.restype = [ctypes.c_void_p], ctypes.c_int   # not in gdr.h
     F.check(L.gdr_debug_tc_trace(F.ptr(buf)))
     fn()
     torch.cuda.synchronize()
