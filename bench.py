@@ -459,7 +459,8 @@ def run_msi_gcn(args):
 
     peak, peak_src = measured_peaks()
     achieved = spmm_bytes / (spmm_ms * 1e-3) / 1e9 if spmm_ms > 0 else 0.0
-    prof = profile_traffic("msi_iteration_r2_full_raw.csv", r"spmm_warp_row_kernel<float, 2") or \
+    prof = profile_traffic("msi_iteration_r3_full_raw.csv", r"spmm_warp_row_kernel<float, 2") or \
+        profile_traffic("msi_iteration_r2_full_raw.csv", r"spmm_warp_row_kernel<float, 2") or \
         profile_traffic("msi_iteration_r1_full_raw.csv", r"spmm_warp_row_kernel<float, 2")
     same_shape = (feats.shape[0], feats.shape[1]) == (29959, 256)
     l2_meas = measure_l2_read_peak(dev)
@@ -581,7 +582,8 @@ def run_rmat_spmm_single(args, steps, warmup):
     b_min = csr.nnz * 8 + 2 * n * d * 4 + (n + 1) * 4
     gbs = b_alg / (ms * 1e-3) / 1e9
     match = (scale, d, args.rmat_edge_factor) == (24, 128, 32)
-    prof = profile_traffic("spmm_rmat24_r2_full_raw.csv", r"spmm_warp_row_kernel<float, 1") or \
+    prof = profile_traffic("spmm_rmat24_r3_full_raw.csv", r"spmm_warp_row_kernel<float, 1") or \
+        profile_traffic("spmm_rmat24_r2_full_raw.csv", r"spmm_warp_row_kernel<float, 1") or \
         profile_traffic("spmm_rmat24_r1b_hub_split_full_raw.csv", r"spmm_warp_row_kernel<float, 1")
     return {"workload": f"rmat scale {scale} edge-factor {args.rmat_edge_factor} d {d} fp32, (A+I)-normalised",
             "nodes": n, "nnz": csr.nnz, "ms_per_spmm": ms, "gedges_per_s": csr.nnz / (ms * 1e-3) / 1e9,

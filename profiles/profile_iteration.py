@@ -24,7 +24,7 @@ if mode == "msi":
     np.random.seed(1)
     torch.manual_seed(1)
     tr = trainer_mod.GCNTrainer(feats, adj, hidden_units=feats.shape[1], num_layers=2, layer_decay=0.3, lr=3e-4,
-                                batch_size=2048, beta_percentile=98.0)
+                                batch_size=2048, beta_percentile=98.0, hoist_layer1=False)   # the bench's `value` path
     batches = [b.to(dev) for b in bench.epoch_batches(feats.shape[0], 2048, 1, 1)[0]]
     for b in batches[:3]:
         tr.iteration(b)
