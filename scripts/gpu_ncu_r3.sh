@@ -9,6 +9,7 @@ run() {  # name, python args...
       python "$@" > gpurun_out/${name}_ncu.log 2>&1 || { echo "$name: ncu run failed"; tail -5 gpurun_out/${name}_ncu.log; return 1; }
   ncu -i gpurun_out/${name}.ncu-rep --page raw --csv > gpurun_out/${name}_full_raw.csv 2> /dev/null
   ls -la gpurun_out/${name}.ncu-rep gpurun_out/${name}_full_raw.csv
+  rm -f gpurun_out/${name}.ncu-rep          # gpurun_out/ travels back only below 64 MiB: keep the CSV export
 }
 run spmm_rmat24_r3 profiles/profile_iteration.py rmat 24 128
 run msi_iteration_r3 profiles/profile_iteration.py msi
